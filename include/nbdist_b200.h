@@ -1,0 +1,199 @@
+/*
+ * nbdist_b200.h — C ABI of the B200-native collective data plane.
+ *
+ * This is the drop-in boundary for the tensor data path that nbdistributed
+ * worker processes drive (dist.all_reduce / broadcast / all_gather /
+ * reduce_scatter / barrier issued by cell code after worker.py's
+ * init_process_group).  The reference has no native code: every byte on this
+ * path moves inside torch's c10d backend ("nccl" | "gloo", selected at
+ * ref:src/nbdistributed/worker.py:135-151).  The entry points below are what a
+ * c10d::Backend (ours: nbdistributed_b200/csrc/c10d_backend.cpp) or any other
+ * host (ctypes, cgo, JNI) binds to replace that backend on one NVLink/NVSwitch
+ * node.  Plain pointers and sizes only; no torch types.
+ *
+ * Model: one process per GPU ("rank").  Each rank owns one ARENA in its HBM
+ * (signal flags + a double-buffered staging area) that every peer maps through
+ * CUDA IPC.  Collectives are single kernels that read/write peer arenas
+ * directly over NVLink and synchronise with per-block release/acquire flags.
+ * User buffers are ordinary device pointers (they need not be registered).
+ *
+ * All functions return NBD_OK (0) or a negative nbd_result code;
+ * nbd_error_string() and nbd_last_error() describe it.  Collectives are
+ * asynchronous with respect to the host: they enqueue work on `stream`
+ * (a cudaStream_t passed as void*; NULL = the legacy default stream).
+ * Every rank of a communicator must issue the same sequence of collectives
+ * with the same counts/dtypes/ops/roots.
+ */
+#ifndef NBDIST_B200_H_
+#define NBDIST_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NBD_VERSION 100 /* 0.1.0 */
+#define NBD_MAX_RANKS 8 /* one NVSwitch node */
+#define NBD_HANDLE_BYTES 256
+
+typedef enum {
+  NBD_OK = 0,
+  NBD_ERR_INVALID_ARGUMENT = -1,
+  NBD_ERR_CUDA = -2,
+  NBD_ERR_NO_PEER_ACCESS = -3,
+  NBD_ERR_TIMEOUT = -4,   /* a peer never arrived at a flag barrier */
+  NBD_ERR_ABORTED = -5,
+  NBD_ERR_UNSUPPORTED = -6, /* dtype/op combination not implemented */
+  NBD_ERR_INTERNAL = -7
+} nbd_result;
+
+/* Element types.  Copy collectives (broadcast, all_gather) are byte moves and
+ * accept any of them; reductions accept all but NBD_BYTES. */
+typedef enum {
+  NBD_F32 = 0,
+  NBD_BF16 = 1,
+  NBD_F16 = 2,
+  NBD_F64 = 3,
+  NBD_I32 = 4,
+  NBD_I64 = 5,
+  NBD_U8 = 6,
+  NBD_I8 = 7,
+  NBD_BYTES = 8 /* opaque 1-byte elements, copy collectives only */
+} nbd_dtype;
+
+/* Reduction operators; numbering follows c10d::ReduceOp::RedOpType
+ * ($TORCH/include/torch/csrc/distributed/c10d/Types.hpp:37-48). */
+typedef enum {
+  NBD_SUM = 0,
+  NBD_AVG = 1, /* floating point only (gloo rejects it; NCCL semantics) */
+  NBD_PROD = 2,
+  NBD_MIN = 3,
+  NBD_MAX = 4,
+  NBD_BAND = 5, /* integer only */
+  NBD_BOR = 6,  /* integer only */
+  NBD_BXOR = 7  /* integer only */
+} nbd_redop;
+
+typedef struct nbd_comm* nbd_comm_t;
+
+/* ---- library ------------------------------------------------------------ */
+
+/* Version of the loaded library (NBD_VERSION it was built with). */
+int nbd_version(void);
+/* Static description of a result code. */
+const char* nbd_error_string(int result);
+/* Thread-local detail of the last failure in this thread ("" if none). */
+const char* nbd_last_error(void);
+/* Size in bytes of one element of `dtype`, 0 if unknown. */
+size_t nbd_dtype_size(int dtype);
+
+/* ---- communicator: one process per GPU ----------------------------------
+ * Replaces the transport set-up torch does inside init_process_group
+ * (ref:src/nbdistributed/worker.py:151).  Bootstrap is three steps so the
+ * caller can use whatever rendezvous it already has (the c10d Store that
+ * worker.py's init_process_group creates):
+ *   1. nbd_comm_create       allocate the arena on `device`
+ *   2. nbd_comm_get_handle   serialise this rank's IPC handle (NBD_HANDLE_BYTES)
+ *      ... caller all-gathers the handles over its store ...
+ *   3. nbd_comm_connect      map every peer's arena
+ * stage_bytes = size of the staging area (0 = default, 256 MiB; rounded up to
+ * 2 MiB).  Larger messages are pipelined through it in chunks. */
+int nbd_comm_create(nbd_comm_t* comm, int rank, int world_size, int device,
+                    size_t stage_bytes);
+int nbd_comm_get_handle(nbd_comm_t comm, void* handle_out /*NBD_HANDLE_BYTES*/);
+/* all_handles: world_size consecutive handles, index = rank. */
+int nbd_comm_connect(nbd_comm_t comm, const void* all_handles);
+/* Replaces the transport teardown of dist.destroy_process_group
+ * (ref:src/nbdistributed/worker.py:578).  Never blocks on peers. */
+int nbd_comm_destroy(nbd_comm_t comm);
+/* Ask in-flight kernels of this rank to leave their flag waits
+ * (c10d::Backend::abort).  The communicator is unusable afterwards. */
+int nbd_comm_abort(nbd_comm_t comm);
+/* NBD_OK, or the asynchronous error a kernel reported (timeout/abort). */
+int nbd_comm_async_error(nbd_comm_t comm);
+int nbd_comm_rank(nbd_comm_t comm);
+int nbd_comm_world_size(nbd_comm_t comm);
+/* Flag-wait watchdog in milliseconds (default 600000; 0 = wait forever). */
+int nbd_comm_set_timeout_ms(nbd_comm_t comm, uint64_t timeout_ms);
+/* Tuning knobs: "blocks" (max CTAs per collective), "ar1_max_bytes"
+ * (one-shot/two-shot all-reduce switch), "bcast_direct_max_bytes",
+ * "chunk_bytes" (pipeline chunk).  value 0 restores the default. */
+int nbd_comm_set_tunable(nbd_comm_t comm, const char* name, uint64_t value);
+int nbd_comm_get_tunable(nbd_comm_t comm, const char* name, uint64_t* value);
+
+/* ---- emulated ranks: R ranks on ONE device, one process -------------------
+ * The same device code as above, with every "peer" arena living on the same
+ * GPU and all R ranks executed by one cooperative launch (grid.y = rank).
+ * This is how the single-GPU parity tests and the 1-GPU bench row (local
+ * copy / k-way reduce against HBM) run; it has no counterpart in the
+ * reference.  comms_out receives world_size communicators (index = rank)
+ * that must only be used with the nbd_emu_* calls below and destroyed with
+ * nbd_emu_destroy(comms_out[0]). */
+int nbd_emu_create(nbd_comm_t* comms_out, int world_size, int device,
+                   size_t stage_bytes);
+int nbd_emu_destroy(nbd_comm_t any_rank_comm);
+
+/* ---- collectives ---------------------------------------------------------
+ * count is in elements of `dtype` unless stated otherwise. */
+
+/* dist.all_reduce(tensor, op)  — $TORCH/distributed/distributed_c10d.py:2979
+ * -> Backend::allreduce (Backend.hpp:148); called from cell code
+ * (ref:README.md:109).  recv[i] = op over ranks 0..N-1 (ascending, fixed
+ * order; bf16/f16 accumulate in fp32 and round once).  send may equal recv. */
+int nbd_all_reduce(nbd_comm_t comm, const void* send, void* recv, size_t count,
+                   int dtype, int op, void* stream);
+
+/* dist.broadcast(tensor, src) — distributed_c10d.py:2927 -> Backend::broadcast
+ * (Backend.hpp:140); ref:README.md:122-123.  In place: root's buf is read,
+ * every other rank's buf is overwritten. */
+int nbd_broadcast(nbd_comm_t comm, void* buf, size_t count, int dtype, int root,
+                  void* stream);
+
+/* dist.all_gather_into_tensor(out, in) — distributed_c10d.py:4091 ->
+ * Backend::_allgather_base (Backend.hpp:200).  recv holds world_size*send_count
+ * elements; recv[r*send_count ...] = rank r's send.  send may alias its own
+ * slot of recv. */
+int nbd_all_gather(nbd_comm_t comm, const void* send, void* recv,
+                   size_t send_count, int dtype, void* stream);
+
+/* dist.reduce_scatter_tensor(out, in, op) — distributed_c10d.py:4563 ->
+ * Backend::_reduce_scatter_base (Backend.hpp:269).  send holds
+ * world_size*recv_count elements; recv = op over ranks of send[rank slot]. */
+int nbd_reduce_scatter(nbd_comm_t comm, const void* send, void* recv,
+                       size_t recv_count, int dtype, int op, void* stream);
+
+/* dist.barrier() — ref:src/nbdistributed/worker.py:214 (from %sync) ->
+ * Backend::barrier (Backend.hpp:382).  Enqueues a flag barrier on `stream`;
+ * the caller synchronises the stream if it wants host-side semantics. */
+int nbd_barrier(nbd_comm_t comm, void* stream);
+
+/* Emulated-rank forms: one call runs the collective for ALL ranks of an
+ * nbd_emu_create() group.  sends/recvs/bufs are arrays of world_size device
+ * pointers (index = rank). */
+int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends,
+                       void* const* recvs, size_t count, int dtype, int op,
+                       void* stream);
+int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count,
+                      int dtype, int root, void* stream);
+int nbd_emu_all_gather(nbd_comm_t any, const void* const* sends,
+                       void* const* recvs, size_t send_count, int dtype,
+                       void* stream);
+int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends,
+                           void* const* recvs, size_t recv_count, int dtype,
+                           int op, void* stream);
+int nbd_emu_barrier(nbd_comm_t any, void* stream);
+
+/* ---- introspection for benches/tests ------------------------------------- */
+
+/* Number of kernels this library has launched in this process so far. */
+uint64_t nbd_launch_count(void);
+/* Name of the algorithm the last collective on `comm` used
+ * ("ar_oneshot", "ar_twoshot", "bcast_direct", "bcast_scatter", ...). */
+const char* nbd_last_algo(nbd_comm_t comm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBDIST_B200_H_ */

@@ -1,0 +1,96 @@
+"""In-tree build of the two native pieces.
+
+* ``libnbdist_b200.so`` — the C-ABI collective library (include/nbdist_b200.h),
+  plain nvcc, sm_100a only, no torch.
+* ``_c10d_b200.so`` — the c10d::Backend glue that torch.distributed loads; it
+  calls the C ABI and is built against the installed torch headers.
+
+Both land next to this file so they travel with the source tree (the GPU box
+receives built .so files; a JIT cache under ~/.cache would not).
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+import sysconfig
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libnbdist_b200.so")
+C10D = os.path.join(HERE, "_c10d_b200.so")
+
+NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found; nbdistributed_b200 needs the CUDA toolkit to build")
+
+
+def _newer(target: str, sources: list[str]) -> bool:
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.getmtime(s) <= t for s in sources)
+
+
+def _sources(exts: tuple[str, ...]) -> list[str]:
+    out = [os.path.join(ROOT, "include", "nbdist_b200.h")]
+    for name in sorted(os.listdir(CSRC)):
+        if name.endswith(exts):
+            out.append(os.path.join(CSRC, name))
+    return out
+
+
+def build_lib(force: bool = False, verbose: bool = False) -> str:
+    """Compile the C-ABI library for sm_100a."""
+    cu = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if n.endswith(".cu")]
+    deps = _sources((".cu", ".cuh", ".h"))
+    if not force and _newer(LIB, deps):
+        return LIB
+    cmd = [_nvcc(), *NVCC_ARCH, "-lineinfo", "-O3", "-std=c++17", "-shared", "-Xcompiler", "-fPIC",
+           "-I", os.path.join(ROOT, "include"), "-o", LIB, *cu]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+        print(" ".join(cmd), file=sys.stderr)
+    subprocess.run(cmd, check=True)
+    return LIB
+
+
+def build_c10d(force: bool = False, verbose: bool = False) -> str:
+    """Compile the c10d::Backend glue against the installed torch (host C++ only)."""
+    src = os.path.join(CSRC, "c10d_backend.cpp")
+    deps = [src, os.path.join(ROOT, "include", "nbdist_b200.h")]
+    if not force and _newer(C10D, deps):
+        return C10D
+    import torch
+    from torch.utils import cpp_extension as ce
+
+    torch_lib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    inc = [*ce.include_paths(device_type="cuda"), sysconfig.get_paths()["include"], os.path.join(ROOT, "include")]
+    cxx = os.environ.get("CXX", "g++")
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden",
+           "-DTORCH_EXTENSION_NAME=_c10d_b200", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
+           *[f"-I{p}" for p in inc], src, "-o", C10D,
+           f"-L{torch_lib}", f"-Wl,-rpath,{torch_lib}",
+           "-ltorch_python", "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-lc10", "-lc10_cuda", "-ldl"]
+    if verbose:
+        print(" ".join(cmd), file=sys.stderr)
+    subprocess.run(cmd, check=True)
+    return C10D
+
+
+def build_all(force: bool = False, verbose: bool = False) -> None:
+    build_lib(force, verbose)
+    if os.path.exists(os.path.join(CSRC, "c10d_backend.cpp")):
+        build_c10d(force, verbose)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv, verbose=True)

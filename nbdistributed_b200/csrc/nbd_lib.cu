@@ -1,0 +1,852 @@
+// nbd_lib.cu — host side of the C ABI in include/nbdist_b200.h: arena
+// allocation, CUDA-IPC peer mapping, algorithm/grid/chunk selection, kernel
+// launches for real ranks (one process per GPU) and emulated ranks (all ranks
+// in one cooperative launch on one GPU).
+//
+// Replaces, for one NVLink/NVSwitch node, the transport that torch's "nccl"
+// backend provides behind ref:src/nbdistributed/worker.py:151.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <string>
+
+#include "../../include/nbdist_b200.h"
+#include "nbd_kernels.cuh"
+
+using namespace nbd;
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+static thread_local char g_last_error[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define NBD_CUDA(call)                                                                      \
+  do {                                                                                      \
+    cudaError_t e__ = (call);                                                               \
+    if (e__ != cudaSuccess)                                                                 \
+      return fail(NBD_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                  __FILE__, __LINE__);                                                      \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool changed = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) changed = (cudaSetDevice(dev) == cudaSuccess);
+  }
+  ~DeviceGuard() {
+    if (changed) cudaSetDevice(prev);
+  }
+};
+
+// ---------------------------------------------------------------------------
+// communicator
+// ---------------------------------------------------------------------------
+struct EmuGroup;
+
+struct nbd_comm {
+  int rank = 0, world = 1, device = 0;
+  int num_sms = 0;
+  bool emu = false, connected = false, dead = false;
+  EmuGroup* group = nullptr;
+  char* arena = nullptr;
+  size_t arena_bytes = 0, stage_bytes = 0;
+  LocalState* state = nullptr;
+  HostMailbox* mbox = nullptr;      // host pointer (pinned, mapped)
+  HostMailbox* mbox_dev = nullptr;  // device alias
+  void* peer_base[kMaxRanks] = {};
+  RankCtx ctx = {};
+  // tunables (0 = default)
+  uint64_t t_blocks = 0, t_ar1_max = 0, t_bcast_direct_max = 0, t_chunk = 0;
+  uint64_t timeout_ms = 600000;
+  const char* last_algo = "none";
+};
+
+struct EmuGroup {
+  int world = 0;
+  nbd_comm* comms[kMaxRanks] = {};
+};
+
+struct Handle {  // serialised into NBD_HANDLE_BYTES
+  uint32_t magic, version;
+  int32_t rank, world;
+  int64_t pid;
+  uint64_t hostid, arena_bytes, stage_bytes;
+  char pci[32];
+  cudaIpcMemHandle_t ipc;
+};
+static_assert(sizeof(Handle) <= NBD_HANDLE_BYTES, "handle too large");
+static const uint32_t kMagic = 0x4e424432u;  // "NBD2"
+
+static uint64_t host_id() {
+  char name[256] = {0};
+  gethostname(name, sizeof(name) - 1);
+  uint64_t h = 1469598103934665603ull;
+  for (const char* p = name; *p; ++p) h = (h ^ (unsigned char)*p) * 1099511628211ull;
+  // boot id distinguishes containers that share a hostname but not /dev/shm
+  FILE* f = fopen("/proc/sys/kernel/random/boot_id", "r");
+  if (f) {
+    char b[64] = {0};
+    if (fgets(b, sizeof(b), f))
+      for (const char* p = b; *p; ++p) h = (h ^ (unsigned char)*p) * 1099511628211ull;
+    fclose(f);
+  }
+  return h;
+}
+
+static const size_t kDefaultStage = 256ull << 20;
+static const size_t kStageAlign = 2ull << 20;
+
+static int alloc_rank(nbd_comm* c, size_t stage_bytes) {
+  if (stage_bytes == 0) {
+    const char* e = getenv("NBDIST_B200_STAGE_BYTES");
+    stage_bytes = e ? strtoull(e, nullptr, 0) : kDefaultStage;
+    if (stage_bytes == 0) stage_bytes = kDefaultStage;
+  }
+  stage_bytes = (stage_bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
+  c->stage_bytes = stage_bytes;
+  c->arena_bytes = kFlagBytes + stage_bytes;
+  cudaDeviceProp prop;
+  NBD_CUDA(cudaGetDeviceProperties(&prop, c->device));
+  c->num_sms = prop.multiProcessorCount;
+  NBD_CUDA(cudaMalloc((void**)&c->arena, c->arena_bytes));
+  NBD_CUDA(cudaMemset(c->arena, 0, kFlagBytes));
+  NBD_CUDA(cudaMalloc((void**)&c->state, sizeof(LocalState)));
+  NBD_CUDA(cudaMemset(c->state, 0, sizeof(LocalState)));
+  NBD_CUDA(cudaHostAlloc((void**)&c->mbox, sizeof(HostMailbox), cudaHostAllocMapped | cudaHostAllocPortable));
+  c->mbox->error = 0;
+  c->mbox->abort = 0;
+  NBD_CUDA(cudaHostGetDevicePointer((void**)&c->mbox_dev, c->mbox, 0));
+  NBD_CUDA(cudaDeviceSynchronize());
+  const char* t = getenv("NBDIST_B200_TIMEOUT_MS");
+  if (t) c->timeout_ms = strtoull(t, nullptr, 0);
+  const char* b = getenv("NBDIST_B200_BLOCKS");
+  if (b) c->t_blocks = strtoull(b, nullptr, 0);
+  const char* ck = getenv("NBDIST_B200_CHUNK_BYTES");
+  if (ck) c->t_chunk = strtoull(ck, nullptr, 0);
+  const char* a1 = getenv("NBDIST_B200_AR1_MAX_BYTES");
+  if (a1) c->t_ar1_max = strtoull(a1, nullptr, 0);
+  const char* bd = getenv("NBDIST_B200_BCAST_DIRECT_MAX_BYTES");
+  if (bd) c->t_bcast_direct_max = strtoull(bd, nullptr, 0);
+  return NBD_OK;
+}
+
+static void fill_ctx(nbd_comm* c) {
+  RankCtx& x = c->ctx;
+  x.rank = c->rank;
+  x.world = c->world;
+  for (int p = 0; p < kMaxRanks; ++p) {
+    char* base = (char*)c->peer_base[p];
+    x.flags[p] = base ? (u64*)base : nullptr;
+    x.stage[p] = base ? base + kFlagBytes : nullptr;
+  }
+  x.state = c->state;
+  x.mbox = c->mbox_dev;
+  x.half_bytes = (c->stage_bytes / 2) / kUnit * kUnit;
+  x.timeout_ns = c->timeout_ms * 1000000ull;
+}
+
+static void free_rank(nbd_comm* c) {
+  if (c->mbox) c->mbox->abort = 1;  // let any stuck flag wait leave before cudaFree's implicit sync
+  if (!c->emu) {
+    for (int p = 0; p < c->world; ++p)
+      if (p != c->rank && c->peer_base[p]) cudaIpcCloseMemHandle(c->peer_base[p]);
+  }
+  if (c->arena) cudaFree(c->arena);
+  if (c->state) cudaFree(c->state);
+  if (c->mbox) cudaFreeHost(c->mbox);
+}
+
+extern "C" {
+
+int nbd_version(void) { return NBD_VERSION; }
+
+const char* nbd_error_string(int r) {
+  switch (r) {
+    case NBD_OK: return "ok";
+    case NBD_ERR_INVALID_ARGUMENT: return "invalid argument";
+    case NBD_ERR_CUDA: return "CUDA runtime error";
+    case NBD_ERR_NO_PEER_ACCESS: return "peer GPU is not reachable over NVLink/PCIe P2P";
+    case NBD_ERR_TIMEOUT: return "timed out waiting for a peer at a flag barrier";
+    case NBD_ERR_ABORTED: return "communicator aborted";
+    case NBD_ERR_UNSUPPORTED: return "unsupported dtype/op combination";
+    case NBD_ERR_INTERNAL: return "internal error";
+    default: return "unknown error";
+  }
+}
+
+const char* nbd_last_error(void) { return g_last_error; }
+
+size_t nbd_dtype_size(int dtype) {
+  switch (dtype) {
+    case NBD_F32: case NBD_I32: return 4;
+    case NBD_BF16: case NBD_F16: return 2;
+    case NBD_F64: case NBD_I64: return 8;
+    case NBD_U8: case NBD_I8: case NBD_BYTES: return 1;
+    default: return 0;
+  }
+}
+
+uint64_t nbd_launch_count(void) { return g_launches.load(); }
+
+int nbd_comm_create(nbd_comm_t* out, int rank, int world, int device, size_t stage_bytes) {
+  if (!out) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (world < 1 || world > kMaxRanks) return fail(NBD_ERR_INVALID_ARGUMENT, "world_size %d not in [1,%d]", world, kMaxRanks);
+  if (rank < 0 || rank >= world) return fail(NBD_ERR_INVALID_ARGUMENT, "rank %d not in [0,%d)", rank, world);
+  int ndev = 0;
+  NBD_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return fail(NBD_ERR_INVALID_ARGUMENT, "device %d not in [0,%d)", device, ndev);
+  DeviceGuard g(device);
+  nbd_comm* c = new nbd_comm();
+  c->rank = rank;
+  c->world = world;
+  c->device = device;
+  int rc = alloc_rank(c, stage_bytes);
+  if (rc != NBD_OK) {
+    free_rank(c);
+    delete c;
+    return rc;
+  }
+  c->peer_base[rank] = c->arena;
+  if (world == 1) {
+    fill_ctx(c);
+    c->connected = true;
+  }
+  *out = c;
+  return NBD_OK;
+}
+
+int nbd_comm_get_handle(nbd_comm_t c, void* handle_out) {
+  if (!c || !handle_out) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL argument");
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "emulated communicators have no IPC handle");
+  DeviceGuard g(c->device);
+  Handle h;
+  memset(&h, 0, sizeof(h));
+  h.magic = kMagic;
+  h.version = NBD_VERSION;
+  h.rank = c->rank;
+  h.world = c->world;
+  h.pid = (int64_t)getpid();
+  h.hostid = host_id();
+  h.arena_bytes = c->arena_bytes;
+  h.stage_bytes = c->stage_bytes;
+  NBD_CUDA(cudaDeviceGetPCIBusId(h.pci, sizeof(h.pci), c->device));
+  NBD_CUDA(cudaIpcGetMemHandle(&h.ipc, c->arena));
+  memset(handle_out, 0, NBD_HANDLE_BYTES);
+  memcpy(handle_out, &h, sizeof(h));
+  return NBD_OK;
+}
+
+int nbd_comm_connect(nbd_comm_t c, const void* all_handles) {
+  if (!c || !all_handles) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL argument");
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "emulated communicators are connected at creation");
+  if (c->connected) return NBD_OK;
+  DeviceGuard g(c->device);
+  const uint64_t me = host_id();
+  for (int p = 0; p < c->world; ++p) {
+    if (p == c->rank) continue;
+    Handle h;
+    memcpy(&h, (const char*)all_handles + (size_t)p * NBD_HANDLE_BYTES, sizeof(h));
+    if (h.magic != kMagic || h.version != NBD_VERSION)
+      return fail(NBD_ERR_INVALID_ARGUMENT, "handle %d: bad magic/version (%#x/%u)", p, h.magic, h.version);
+    if (h.rank != p || h.world != c->world)
+      return fail(NBD_ERR_INVALID_ARGUMENT, "handle %d describes rank %d of %d", p, h.rank, h.world);
+    if (h.hostid != me)
+      return fail(NBD_ERR_NO_PEER_ACCESS, "rank %d is on another host; this backend is single-node (NVLink/NVSwitch)", p);
+    if (h.stage_bytes != c->stage_bytes)
+      return fail(NBD_ERR_INVALID_ARGUMENT, "rank %d has stage_bytes %llu, this rank %llu", p,
+                  (unsigned long long)h.stage_bytes, (unsigned long long)c->stage_bytes);
+    if (h.pid == (int64_t)getpid())
+      return fail(NBD_ERR_INVALID_ARGUMENT, "rank %d lives in this process; use one process per GPU (or nbd_emu_*)", p);
+    int pdev = -1;
+    if (cudaDeviceGetByPCIBusId(&pdev, h.pci) == cudaSuccess && pdev >= 0) {
+      if (pdev == c->device)
+        return fail(NBD_ERR_INVALID_ARGUMENT, "rank %d shares GPU %s with this rank; ranks must own distinct GPUs", p, h.pci);
+      int can = 0;
+      NBD_CUDA(cudaDeviceCanAccessPeer(&can, c->device, pdev));
+      if (!can) return fail(NBD_ERR_NO_PEER_ACCESS, "GPU %d cannot access peer GPU %d (%s)", c->device, pdev, h.pci);
+    } else {
+      cudaGetLastError();  // peer not visible in this process (CUDA_VISIBLE_DEVICES); let IPC decide
+    }
+    void* ptr = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&ptr, h.ipc, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(NBD_ERR_NO_PEER_ACCESS, "cudaIpcOpenMemHandle(rank %d, %s): %s", p, h.pci, cudaGetErrorString(e));
+    }
+    c->peer_base[p] = ptr;
+  }
+  fill_ctx(c);
+  c->connected = true;
+  return NBD_OK;
+}
+
+int nbd_comm_destroy(nbd_comm_t c) {
+  if (!c) return NBD_OK;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_destroy for emulated communicators");
+  DeviceGuard g(c->device);
+  free_rank(c);
+  delete c;
+  return NBD_OK;
+}
+
+int nbd_comm_abort(nbd_comm_t c) {
+  if (!c) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  c->mbox->abort = 1;
+  c->dead = true;
+  return NBD_OK;
+}
+
+int nbd_comm_async_error(nbd_comm_t c) {
+  if (!c) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  const uint32_t e = ((volatile HostMailbox*)c->mbox)->error;
+  if (e == 0) return NBD_OK;
+  c->dead = true;
+  return fail(-(int)e, "rank %d: a collective kernel gave up at a flag barrier (%s)", c->rank, nbd_error_string(-(int)e));
+}
+
+int nbd_comm_rank(nbd_comm_t c) { return c ? c->rank : -1; }
+int nbd_comm_world_size(nbd_comm_t c) { return c ? c->world : -1; }
+
+int nbd_comm_set_timeout_ms(nbd_comm_t c, uint64_t ms) {
+  if (!c) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  c->timeout_ms = ms;
+  c->ctx.timeout_ns = ms * 1000000ull;
+  return NBD_OK;
+}
+
+static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
+  if (!strcmp(name, "blocks")) return &c->t_blocks;
+  if (!strcmp(name, "ar1_max_bytes")) return &c->t_ar1_max;
+  if (!strcmp(name, "bcast_direct_max_bytes")) return &c->t_bcast_direct_max;
+  if (!strcmp(name, "chunk_bytes")) return &c->t_chunk;
+  return nullptr;
+}
+
+int nbd_comm_set_tunable(nbd_comm_t c, const char* name, uint64_t value) {
+  if (!c || !name) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL argument");
+  uint64_t* s = tunable_slot(c, name);
+  if (!s) return fail(NBD_ERR_INVALID_ARGUMENT, "unknown tunable '%s'", name);
+  *s = value;
+  return NBD_OK;
+}
+
+int nbd_comm_get_tunable(nbd_comm_t c, const char* name, uint64_t* value) {
+  if (!c || !name || !value) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL argument");
+  uint64_t* s = tunable_slot(c, name);
+  if (!s) return fail(NBD_ERR_INVALID_ARGUMENT, "unknown tunable '%s'", name);
+  *value = *s;
+  return NBD_OK;
+}
+
+const char* nbd_last_algo(nbd_comm_t c) { return c ? c->last_algo : "none"; }
+
+// ---- emulated ranks -------------------------------------------------------
+
+int nbd_emu_create(nbd_comm_t* out, int world, int device, size_t stage_bytes) {
+  if (!out) return fail(NBD_ERR_INVALID_ARGUMENT, "comms_out is NULL");
+  if (world < 1 || world > kMaxRanks) return fail(NBD_ERR_INVALID_ARGUMENT, "world_size %d not in [1,%d]", world, kMaxRanks);
+  int ndev = 0;
+  NBD_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return fail(NBD_ERR_INVALID_ARGUMENT, "device %d not in [0,%d)", device, ndev);
+  DeviceGuard g(device);
+  int coop = 0;
+  NBD_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
+  if (!coop) return fail(NBD_ERR_UNSUPPORTED, "device %d lacks cooperative launch", device);
+  EmuGroup* grp = new EmuGroup();
+  grp->world = world;
+  int rc = NBD_OK;
+  for (int r = 0; r < world && rc == NBD_OK; ++r) {
+    nbd_comm* c = new nbd_comm();
+    c->rank = r;
+    c->world = world;
+    c->device = device;
+    c->emu = true;
+    c->group = grp;
+    grp->comms[r] = c;
+    rc = alloc_rank(c, stage_bytes);
+  }
+  if (rc != NBD_OK) {
+    for (int r = 0; r < world; ++r)
+      if (grp->comms[r]) {
+        free_rank(grp->comms[r]);
+        delete grp->comms[r];
+      }
+    delete grp;
+    return rc;
+  }
+  for (int r = 0; r < world; ++r) {
+    nbd_comm* c = grp->comms[r];
+    for (int p = 0; p < world; ++p) c->peer_base[p] = grp->comms[p]->arena;
+    fill_ctx(c);
+    c->connected = true;
+    out[r] = c;
+  }
+  return NBD_OK;
+}
+
+int nbd_emu_destroy(nbd_comm_t any) {
+  if (!any) return NBD_OK;
+  if (!any->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "not an emulated communicator");
+  EmuGroup* grp = any->group;
+  DeviceGuard g(any->device);
+  for (int r = 0; r < grp->world; ++r) {
+    free_rank(grp->comms[r]);
+    delete grp->comms[r];
+  }
+  delete grp;
+  return NBD_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// planning: algorithm, chunking, grid
+// ---------------------------------------------------------------------------
+static inline u64 floor_to(u64 x, u64 m) { return x / m * m; }
+static inline u64 ceil_div(u64 a, u64 b) { return (a + b - 1) / b; }
+
+struct Plan {
+  OpParams op;
+  int nblocks;
+};
+
+// CTAs: enough that each handles >= 4 units per thread, at most the number that
+// is guaranteed co-resident (flag waits need every CTA of every rank running).
+// max_blocks is that bound, computed per kernel by occupancy_cap().
+static int pick_blocks(const nbd_comm* c, u64 units_per_block_span, int emu_world) {
+  u64 cap = (u64)c->num_sms * kMinBlocksPerSM;
+  if (emu_world > 1) cap /= (u64)emu_world;
+  if (c->t_blocks && c->t_blocks < cap) cap = c->t_blocks;
+  if (cap > (u64)kMaxBlocks) cap = kMaxBlocks;
+  if (cap < 1) cap = 1;
+  u64 want = ceil_div(units_per_block_span, (u64)kThreads * 4);
+  if (want < 1) want = 1;
+  return (int)(want < cap ? want : cap);
+}
+
+static const u64 kDefChunkAR = 32ull << 20;    // message bytes per step
+static const u64 kDefChunkShard = 8ull << 20;  // shard bytes per step (rs / ag)
+static const u64 kDefChunkBcast = 32ull << 20;
+
+static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
+  Plan p;
+  memset(&p, 0, sizeof(p));
+  const int N = c->world;
+  const u64 half = c->ctx.half_bytes;
+  const u64 ar1_max = c->t_ar1_max ? c->t_ar1_max : (N == 2 ? ~0ull : (512ull << 10));
+  p.op.bytes = bytes;
+  p.op.op = op;
+  p.op.avg = (op == NBD_AVG);
+  p.op.world = N;
+  if (bytes <= ar1_max) {
+    p.op.algo = 1;
+    u64 cap = floor_to(half / N, kUnit);
+    u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkAR / N;
+    if (chunk < kUnit) chunk = kUnit;
+    if (chunk > cap) chunk = cap;
+    p.op.chunk_bytes = chunk;
+    p.op.nchunks = (u32)ceil_div(bytes, chunk);
+    p.nblocks = pick_blocks(c, ceil_div(bytes < chunk ? bytes : chunk, kUnit), emu_world);
+    c->last_algo = "ar_oneshot";
+  } else {
+    p.op.algo = 2;
+    // (N+1) slots of ceil(units/N) units must fit in one half
+    u64 cap = floor_to((half / (N + 1) - kUnit) * N, (u64)kUnit * N);
+    u64 chunk = c->t_chunk ? floor_to(c->t_chunk, (u64)kUnit * N) : kDefChunkAR;
+    if (chunk < (u64)kUnit * N) chunk = (u64)kUnit * N;
+    if (chunk > cap) chunk = cap;
+    p.op.chunk_bytes = chunk;
+    p.op.nchunks = (u32)ceil_div(bytes, chunk);
+    p.nblocks = pick_blocks(c, ceil_div(ceil_div(bytes < chunk ? bytes : chunk, kUnit), N), emu_world);
+    c->last_algo = "ar_twoshot";
+  }
+  return p;
+}
+
+static Plan plan_reduce_scatter(nbd_comm* c, u64 shard_bytes, int op, int emu_world) {
+  Plan p;
+  memset(&p, 0, sizeof(p));
+  const int N = c->world;
+  const u64 half = c->ctx.half_bytes;
+  p.op.bytes = shard_bytes;
+  p.op.op = op;
+  p.op.avg = (op == NBD_AVG);
+  p.op.world = N;
+  u64 cap = floor_to(half / N, kUnit);
+  u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkShard;
+  if (chunk < kUnit) chunk = kUnit;
+  if (chunk > cap) chunk = cap;
+  p.op.chunk_bytes = chunk;
+  p.op.nchunks = (u32)ceil_div(shard_bytes, chunk);
+  p.nblocks = pick_blocks(c, ceil_div(shard_bytes < chunk ? shard_bytes : chunk, kUnit), emu_world);
+  c->last_algo = "reduce_scatter_push";
+  return p;
+}
+
+static Plan plan_all_gather(nbd_comm* c, u64 shard_bytes, int emu_world) {
+  Plan p;
+  memset(&p, 0, sizeof(p));
+  const u64 half = c->ctx.half_bytes;
+  p.op.bytes = shard_bytes;
+  p.op.world = c->world;
+  u64 cap = floor_to(half, kUnit);
+  u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkShard;
+  if (chunk < kUnit) chunk = kUnit;
+  if (chunk > cap) chunk = cap;
+  p.op.chunk_bytes = chunk;
+  p.op.nchunks = (u32)ceil_div(shard_bytes, chunk);
+  p.nblocks = pick_blocks(c, ceil_div(shard_bytes < chunk ? shard_bytes : chunk, kUnit), emu_world);
+  c->last_algo = "all_gather_pull";
+  return p;
+}
+
+static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
+  Plan p;
+  memset(&p, 0, sizeof(p));
+  const int N = c->world;
+  const u64 half = c->ctx.half_bytes;
+  const u64 direct_max = c->t_bcast_direct_max ? c->t_bcast_direct_max : (N <= 2 ? ~0ull : (256ull << 10));
+  p.op.bytes = bytes;
+  p.op.root = root;
+  p.op.world = N;
+  if (bytes <= direct_max) {
+    p.op.algo = 0;
+    u64 cap = floor_to(half, kUnit);
+    u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkBcast;
+    if (chunk < kUnit) chunk = kUnit;
+    if (chunk > cap) chunk = cap;
+    p.op.chunk_bytes = chunk;
+    p.op.nchunks = (u32)ceil_div(bytes, chunk);
+    p.nblocks = pick_blocks(c, ceil_div(bytes < chunk ? bytes : chunk, kUnit), emu_world);
+    c->last_algo = "bcast_direct";
+  } else {
+    p.op.algo = 1;
+    const u64 nsh = (u64)(N - 1);
+    u64 cap = floor_to((half - kUnit) * nsh, (u64)kUnit * nsh);
+    u64 chunk = c->t_chunk ? floor_to(c->t_chunk, (u64)kUnit * nsh) : floor_to(kDefChunkBcast, (u64)kUnit * nsh);
+    if (chunk < (u64)kUnit * nsh) chunk = (u64)kUnit * nsh;
+    if (chunk > cap) chunk = cap;
+    p.op.chunk_bytes = chunk;
+    p.op.nchunks = (u32)ceil_div(bytes, chunk);
+    p.nblocks = pick_blocks(c, ceil_div(ceil_div(bytes < chunk ? bytes : chunk, kUnit), nsh), emu_world);
+    c->last_algo = "bcast_scatter";
+  }
+  return p;
+}
+
+// ---------------------------------------------------------------------------
+// launch
+// ---------------------------------------------------------------------------
+#define NBD_SWITCH_DTYPE(dtype, ...)                                         \
+  switch (dtype) {                                                           \
+    case NBD_F32: { typedef float T; __VA_ARGS__; } break;                   \
+    case NBD_BF16: { typedef __nv_bfloat16 T; __VA_ARGS__; } break;          \
+    case NBD_F16: { typedef __half T; __VA_ARGS__; } break;                  \
+    case NBD_F64: { typedef double T; __VA_ARGS__; } break;                  \
+    case NBD_I32: { typedef int32_t T; __VA_ARGS__; } break;                 \
+    case NBD_I64: { typedef int64_t T; __VA_ARGS__; } break;                 \
+    case NBD_U8: { typedef uint8_t T; __VA_ARGS__; } break;                  \
+    case NBD_I8: { typedef int8_t T; __VA_ARGS__; } break;                   \
+    default: rc = fail(NBD_ERR_UNSUPPORTED, "dtype %d cannot be reduced", dtype); \
+  }
+
+enum Kind { K_AR1, K_AR2, K_RS };
+
+template <typename T, bool SUM, int NCTX>
+static const void* reduce_kernel(Kind k) {
+  switch (k) {
+    case K_AR1: return (const void*)k_allreduce_oneshot<T, SUM, NCTX>;
+    case K_AR2: return (const void*)k_allreduce_twoshot<T, SUM, NCTX>;
+    default: return (const void*)k_reduce_scatter<T, SUM, NCTX>;
+  }
+}
+
+template <int NCTX>
+static int launch_any(const void* kernel, int nblocks, int world, cudaStream_t s, Pack<NCTX>& pk, OpParams* op) {
+  void* args[2] = {(void*)&pk, (void*)op};
+  if (NCTX == 1) {
+    NBD_CUDA(cudaLaunchKernel(kernel, dim3(nblocks, 1, 1), dim3(kThreads, 1, 1), args, 0, s));
+  } else {
+    NBD_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(nblocks, world, 1), dim3(kThreads, 1, 1), args, 0, s));
+  }
+  g_launches.fetch_add(1);
+  return NBD_OK;
+}
+
+template <int NCTX>
+static int launch_reduce(Kind k, int dtype, int op, int nblocks, int world, cudaStream_t s, Pack<NCTX>& pk,
+                         OpParams* prm) {
+  int rc = NBD_OK;
+  const bool sum = (op == NBD_SUM || op == NBD_AVG);
+  const void* fn = nullptr;
+  NBD_SWITCH_DTYPE(dtype, fn = sum ? reduce_kernel<T, true, NCTX>(k) : reduce_kernel<T, false, NCTX>(k));
+  if (rc != NBD_OK) return rc;
+  return launch_any<NCTX>(fn, nblocks, world, s, pk, prm);
+}
+
+static int check_usable(nbd_comm* c) {
+  if (!c) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (!c->connected) return fail(NBD_ERR_INVALID_ARGUMENT, "communicator is not connected (call nbd_comm_connect)");
+  if (c->dead) return fail(NBD_ERR_ABORTED, "communicator was aborted or hit an asynchronous error");
+  return nbd_comm_async_error(c);
+}
+
+static int check_reduce_args(int dtype, int op) {
+  const size_t es = nbd_dtype_size(dtype);
+  if (es == 0 || dtype == NBD_BYTES) return fail(NBD_ERR_UNSUPPORTED, "dtype %d cannot be reduced", dtype);
+  const bool is_float = (dtype == NBD_F32 || dtype == NBD_BF16 || dtype == NBD_F16 || dtype == NBD_F64);
+  if (op < NBD_SUM || op > NBD_BXOR) return fail(NBD_ERR_INVALID_ARGUMENT, "unknown reduce op %d", op);
+  if (is_float && (op == NBD_BAND || op == NBD_BOR || op == NBD_BXOR))
+    return fail(NBD_ERR_UNSUPPORTED, "bitwise reduce ops need an integer dtype");
+  if (!is_float && op == NBD_AVG) return fail(NBD_ERR_UNSUPPORTED, "AVG needs a floating-point dtype");
+  return NBD_OK;
+}
+
+// Fills pk for a real rank (NCTX == 1) or every emulated rank.
+static void fill_pack(Pack<1>& pk, nbd_comm* c, const void* send, void* recv) {
+  pk.ctx[0] = c->ctx;
+  pk.buf[0].send = (const char*)send;
+  pk.buf[0].recv = (char*)recv;
+}
+
+static int fill_pack_emu(Pack<kMaxRanks>& pk, EmuGroup* g, const void* const* sends, void* const* recvs) {
+  memset(&pk, 0, sizeof(pk));
+  for (int r = 0; r < g->world; ++r) {
+    int rc = check_usable(g->comms[r]);
+    if (rc != NBD_OK) return rc;
+    pk.ctx[r] = g->comms[r]->ctx;
+    pk.buf[r].send = sends ? (const char*)sends[r] : nullptr;
+    pk.buf[r].recv = recvs ? (char*)recvs[r] : nullptr;
+  }
+  return NBD_OK;
+}
+
+extern "C" {
+
+// ---- real ranks -----------------------------------------------------------
+
+int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int dtype, int op, void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_all_reduce with emulated communicators");
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (count == 0) return NBD_OK;
+  if (!send || !recv) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer");
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const u64 bytes = (u64)count * nbd_dtype_size(dtype);
+  if (c->world == 1) {
+    c->last_algo = "local";
+    if (send != recv) NBD_CUDA(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
+    return NBD_OK;
+  }
+  Plan p = plan_all_reduce(c, bytes, op, 0);
+  Pack<1> pk;
+  fill_pack(pk, c, send, recv);
+  return launch_reduce<1>(p.op.algo == 1 ? K_AR1 : K_AR2, dtype, op, p.nblocks, 1, s, pk, &p.op);
+}
+
+int nbd_reduce_scatter(nbd_comm_t c, const void* send, void* recv, size_t recv_count, int dtype, int op,
+                       void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_reduce_scatter with emulated communicators");
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (recv_count == 0) return NBD_OK;
+  if (!send || !recv) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer");
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const u64 bytes = (u64)recv_count * nbd_dtype_size(dtype);
+  if (c->world == 1) {
+    c->last_algo = "local";
+    if (send != recv) NBD_CUDA(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
+    return NBD_OK;
+  }
+  Plan p = plan_reduce_scatter(c, bytes, op, 0);
+  Pack<1> pk;
+  fill_pack(pk, c, send, recv);
+  return launch_reduce<1>(K_RS, dtype, op, p.nblocks, 1, s, pk, &p.op);
+}
+
+int nbd_all_gather(nbd_comm_t c, const void* send, void* recv, size_t send_count, int dtype, void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_all_gather with emulated communicators");
+  const size_t es = nbd_dtype_size(dtype);
+  if (es == 0) return fail(NBD_ERR_INVALID_ARGUMENT, "unknown dtype %d", dtype);
+  if (send_count == 0) return NBD_OK;
+  if (!send || !recv) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer");
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const u64 bytes = (u64)send_count * es;
+  if (c->world == 1) {
+    c->last_algo = "local";
+    if (send != recv) NBD_CUDA(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
+    return NBD_OK;
+  }
+  Plan p = plan_all_gather(c, bytes, 0);
+  Pack<1> pk;
+  fill_pack(pk, c, send, recv);
+  return launch_any<1>((const void*)k_all_gather<1>, p.nblocks, 1, s, pk, &p.op);
+}
+
+int nbd_broadcast(nbd_comm_t c, void* buf, size_t count, int dtype, int root, void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_broadcast with emulated communicators");
+  const size_t es = nbd_dtype_size(dtype);
+  if (es == 0) return fail(NBD_ERR_INVALID_ARGUMENT, "unknown dtype %d", dtype);
+  if (root < 0 || root >= c->world) return fail(NBD_ERR_INVALID_ARGUMENT, "root %d not in [0,%d)", root, c->world);
+  if (count == 0) return NBD_OK;
+  if (!buf) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer");
+  if (c->world == 1) {
+    c->last_algo = "local";
+    return NBD_OK;
+  }
+  DeviceGuard g(c->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  Plan p = plan_broadcast(c, (u64)count * es, root, 0);
+  Pack<1> pk;
+  fill_pack(pk, c, buf, buf);
+  return launch_any<1>((const void*)k_broadcast<1>, p.nblocks, 1, s, pk, &p.op);
+}
+
+int nbd_barrier(nbd_comm_t c, void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_barrier with emulated communicators");
+  if (c->world == 1) return NBD_OK;
+  DeviceGuard g(c->device);
+  Pack<1> pk;
+  fill_pack(pk, c, nullptr, nullptr);
+  void* args[1] = {(void*)&pk};
+  NBD_CUDA(cudaLaunchKernel((const void*)k_barrier<1>, dim3(1, 1, 1), dim3(kThreads, 1, 1), args, 0,
+                            (cudaStream_t)stream));
+  g_launches.fetch_add(1);
+  c->last_algo = "barrier";
+  return NBD_OK;
+}
+
+// ---- emulated ranks -------------------------------------------------------
+
+static int emu_local_copies(EmuGroup* g, const void* const* sends, void* const* recvs, u64 bytes, cudaStream_t s) {
+  for (int r = 0; r < g->world; ++r)
+    if (sends[r] != recvs[r]) NBD_CUDA(cudaMemcpyAsync(recvs[r], sends[r], bytes, cudaMemcpyDeviceToDevice, s));
+  return NBD_OK;
+}
+
+static int emu_check(nbd_comm_t any, const void* const* a, const void* const* b, bool need_b) {
+  if (!any) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (!any->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "not an emulated communicator");
+  if (!a || (need_b && !b)) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL pointer array");
+  for (int r = 0; r < any->group->world; ++r)
+    if (!a[r] || (need_b && !b[r])) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer for rank %d", r);
+  return NBD_OK;
+}
+
+int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* recvs, size_t count, int dtype,
+                       int op, void* stream) {
+  int rc;
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (any && any->emu && count == 0) return NBD_OK;
+  if ((rc = emu_check(any, sends, (const void* const*)recvs, true)) != NBD_OK) return rc;
+  EmuGroup* g = any->group;
+  nbd_comm* c0 = g->comms[0];
+  DeviceGuard dg(c0->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const u64 bytes = (u64)count * nbd_dtype_size(dtype);
+  if (g->world == 1) return emu_local_copies(g, sends, recvs, bytes, s);
+  Pack<kMaxRanks> pk;
+  if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;
+  Plan p = plan_all_reduce(c0, bytes, op, g->world);
+  for (int r = 1; r < g->world; ++r) g->comms[r]->last_algo = c0->last_algo;
+  return launch_reduce<kMaxRanks>(p.op.algo == 1 ? K_AR1 : K_AR2, dtype, op, p.nblocks, g->world, s, pk, &p.op);
+}
+
+int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends, void* const* recvs, size_t recv_count,
+                           int dtype, int op, void* stream) {
+  int rc;
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (any && any->emu && recv_count == 0) return NBD_OK;
+  if ((rc = emu_check(any, sends, (const void* const*)recvs, true)) != NBD_OK) return rc;
+  EmuGroup* g = any->group;
+  nbd_comm* c0 = g->comms[0];
+  DeviceGuard dg(c0->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const u64 bytes = (u64)recv_count * nbd_dtype_size(dtype);
+  if (g->world == 1) return emu_local_copies(g, sends, recvs, bytes, s);
+  Pack<kMaxRanks> pk;
+  if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;
+  Plan p = plan_reduce_scatter(c0, bytes, op, g->world);
+  return launch_reduce<kMaxRanks>(K_RS, dtype, op, p.nblocks, g->world, s, pk, &p.op);
+}
+
+int nbd_emu_all_gather(nbd_comm_t any, const void* const* sends, void* const* recvs, size_t send_count, int dtype,
+                       void* stream) {
+  int rc;
+  const size_t es = nbd_dtype_size(dtype);
+  if (es == 0) return fail(NBD_ERR_INVALID_ARGUMENT, "unknown dtype %d", dtype);
+  if (any && any->emu && send_count == 0) return NBD_OK;
+  if ((rc = emu_check(any, sends, (const void* const*)recvs, true)) != NBD_OK) return rc;
+  EmuGroup* g = any->group;
+  nbd_comm* c0 = g->comms[0];
+  DeviceGuard dg(c0->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const u64 bytes = (u64)send_count * es;
+  if (g->world == 1) return emu_local_copies(g, sends, recvs, bytes, s);
+  Pack<kMaxRanks> pk;
+  if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;
+  Plan p = plan_all_gather(c0, bytes, g->world);
+  return launch_any<kMaxRanks>((const void*)k_all_gather<kMaxRanks>, p.nblocks, g->world, s, pk, &p.op);
+}
+
+int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count, int dtype, int root, void* stream) {
+  int rc;
+  const size_t es = nbd_dtype_size(dtype);
+  if (es == 0) return fail(NBD_ERR_INVALID_ARGUMENT, "unknown dtype %d", dtype);
+  if (any && any->emu && count == 0) return NBD_OK;
+  if ((rc = emu_check(any, (const void* const*)bufs, nullptr, false)) != NBD_OK) return rc;
+  EmuGroup* g = any->group;
+  if (root < 0 || root >= g->world) return fail(NBD_ERR_INVALID_ARGUMENT, "root %d not in [0,%d)", root, g->world);
+  if (g->world == 1) return NBD_OK;
+  nbd_comm* c0 = g->comms[0];
+  DeviceGuard dg(c0->device);
+  Pack<kMaxRanks> pk;
+  if ((rc = fill_pack_emu(pk, g, (const void* const*)bufs, bufs)) != NBD_OK) return rc;
+  Plan p = plan_broadcast(c0, (u64)count * es, root, g->world);
+  return launch_any<kMaxRanks>((const void*)k_broadcast<kMaxRanks>, p.nblocks, g->world, (cudaStream_t)stream, pk,
+                               &p.op);
+}
+
+int nbd_emu_barrier(nbd_comm_t any, void* stream) {
+  if (!any) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (!any->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "not an emulated communicator");
+  EmuGroup* g = any->group;
+  if (g->world == 1) return NBD_OK;
+  DeviceGuard dg(g->comms[0]->device);
+  Pack<kMaxRanks> pk;
+  int rc = fill_pack_emu(pk, g, nullptr, nullptr);
+  if (rc != NBD_OK) return rc;
+  void* args[1] = {(void*)&pk};
+  NBD_CUDA(cudaLaunchCooperativeKernel((const void*)k_barrier<kMaxRanks>, dim3(1, g->world, 1),
+                                       dim3(kThreads, 1, 1), args, 0, (cudaStream_t)stream));
+  g_launches.fetch_add(1);
+  return NBD_OK;
+}
+
+}  // extern "C"

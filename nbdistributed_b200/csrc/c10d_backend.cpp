@@ -1,0 +1,500 @@
+// c10d_backend.cpp — the c10d::Backend that torch.distributed loads for
+// backend string "b200".  It is glue only: tensor checks, stream/event
+// bookkeeping, IPC-handle exchange over the store torch hands us, and calls
+// into the C ABI (include/nbdist_b200.h) where the sm_100a kernels live.
+//
+// It replaces, for CUDA tensors, the ProcessGroupNCCL instance that
+// ref:src/nbdistributed/worker.py:145-151 selects with backend="nccl":
+// the same user calls (dist.all_reduce / broadcast / all_gather /
+// reduce_scatter / barrier from cell code, ref:src/nbdistributed/worker.py:162,
+// :214) arrive here through c10d::Backend's virtuals
+// ($TORCH/include/torch/csrc/distributed/c10d/Backend.hpp:140-382).
+#include <ATen/cuda/CUDAContext.h>
+#include <ATen/cuda/CUDAEvent.h>
+#include <c10/cuda/CUDACachingAllocator.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <pybind11/chrono.h>
+#include <torch/csrc/distributed/c10d/Backend.hpp>
+#include <torch/csrc/distributed/c10d/Store.hpp>
+#include <torch/csrc/distributed/c10d/Types.hpp>
+#include <torch/csrc/distributed/c10d/Work.hpp>
+#include <torch/extension.h>
+
+#include <chrono>
+#include <mutex>
+#include <thread>
+
+#include "nbdist_b200.h"
+
+namespace {
+
+constexpr const char* kBackendName = "b200";
+
+[[noreturn]] void throw_nbd(int rc, const char* what) {
+  std::string msg = c10::str("[", kBackendName, "] ", what, ": ", nbd_error_string(rc));
+  const char* detail = nbd_last_error();
+  if (detail && *detail) msg += c10::str(" — ", detail);
+  C10_THROW_ERROR(DistBackendError, msg);
+}
+
+#define NBD_CHECK(call, what)       \
+  do {                              \
+    int rc__ = (call);              \
+    if (rc__ != NBD_OK) throw_nbd(rc__, what); \
+  } while (0)
+
+int to_nbd_dtype(at::ScalarType t, bool for_reduce) {
+  switch (t) {
+    case at::kFloat: return NBD_F32;
+    case at::kBFloat16: return NBD_BF16;
+    case at::kHalf: return NBD_F16;
+    case at::kDouble: return NBD_F64;
+    case at::kInt: return NBD_I32;
+    case at::kLong: return NBD_I64;
+    case at::kByte: return NBD_U8;
+    case at::kChar: return NBD_I8;
+    default:
+      TORCH_CHECK(!for_reduce, "[b200] dtype ", t, " cannot be reduced (supported: float32, bfloat16, float16, "
+                  "float64, int32, int64, uint8, int8)");
+      return NBD_BYTES;
+  }
+}
+
+int to_nbd_op(const c10d::ReduceOp& op) {
+  switch (op.op_) {
+    case c10d::ReduceOp::SUM: return NBD_SUM;
+    case c10d::ReduceOp::AVG: return NBD_AVG;
+    case c10d::ReduceOp::PRODUCT: return NBD_PROD;
+    case c10d::ReduceOp::MIN: return NBD_MIN;
+    case c10d::ReduceOp::MAX: return NBD_MAX;
+    case c10d::ReduceOp::BAND: return NBD_BAND;
+    case c10d::ReduceOp::BOR: return NBD_BOR;
+    case c10d::ReduceOp::BXOR: return NBD_BXOR;
+    default: TORCH_CHECK(false, "[b200] unsupported ReduceOp (PREMUL_SUM is NCCL-specific)");
+  }
+}
+
+void check_tensor(const at::Tensor& t) {
+  TORCH_CHECK(t.is_cuda(), "[b200] tensors must be CUDA tensors (this backend is registered for devices=['cuda'])");
+  TORCH_CHECK(!t.is_sparse(), "[b200] sparse tensors are not supported");
+  TORCH_CHECK_VALUE(t.is_contiguous(t.suggest_memory_format()), "Tensors must be contiguous");
+}
+
+// ---------------------------------------------------------------------------
+class WorkB200 : public c10d::Work {
+ public:
+  WorkB200(int rank, c10d::OpType type, const char* title, c10::DeviceIndex dev, nbd_comm_t comm,
+           std::vector<at::Tensor> outputs, bool is_barrier)
+      : c10d::Work(rank, type, title), dev_(dev), comm_(comm), outputs_(std::move(outputs)), is_barrier_(is_barrier) {}
+
+  // record completion on `stream` and publish a CUDA-aware future bound to it
+  void mark_enqueued(c10::cuda::CUDAStream stream) {
+    done_.record(stream);
+    future_ = c10::make_intrusive<at::ivalue::Future>(c10::ListType::create(c10::TensorType::get()),
+                                                      std::vector<c10::Device>{c10::Device(c10::kCUDA, dev_)});
+    c10::cuda::CUDAStreamGuard g(stream);
+    future_->markCompleted(at::IValue(outputs_));
+  }
+
+  bool isCompleted() override { return done_.query(); }
+  bool isSuccess() const override { return nbd_comm_async_error(comm_) == NBD_OK; }
+
+  void synchronize() override {
+    auto cur = c10::cuda::getCurrentCUDAStream(dev_);
+    done_.block(cur);
+    if (is_barrier_) {
+      // dist.barrier() is a host-side rendezvous (as ProcessGroupNCCL does for barrier works)
+      c10::cuda::CUDAGuard g(dev_);
+      C10_CUDA_CHECK(cudaStreamSynchronize(cur));
+      int rc = nbd_comm_async_error(comm_);
+      if (rc != NBD_OK) throw_nbd(rc, "barrier");
+    }
+  }
+
+  bool wait(std::chrono::milliseconds /*timeout*/ = kNoTimeout) override {
+    synchronize();
+    return true;
+  }
+
+  std::vector<at::Tensor> result() override { return outputs_; }
+  c10::intrusive_ptr<c10::ivalue::Future> getFuture() override { return future_; }
+
+ private:
+  c10::DeviceIndex dev_;
+  nbd_comm_t comm_;
+  std::vector<at::Tensor> outputs_;
+  bool is_barrier_;
+  at::cuda::CUDAEvent done_;
+  c10::intrusive_ptr<at::ivalue::Future> future_;
+};
+
+// ---------------------------------------------------------------------------
+class BackendB200 : public c10d::Backend {
+ public:
+  BackendB200(c10::intrusive_ptr<c10d::Store> store, int rank, int size, std::chrono::milliseconds timeout)
+      : c10d::Backend(rank, size), store_(std::move(store)), timeout_(timeout) {
+    TORCH_CHECK(size >= 1 && size <= NBD_MAX_RANKS, "[b200] world_size ", size, " unsupported: this backend drives one "
+                "NVLink/NVSwitch node of at most ", NBD_MAX_RANKS, " GPUs");
+    TORCH_CHECK(at::cuda::is_available(), "[b200] no CUDA device: the b200 backend has no CPU fallback "
+                "(use 'gloo' for CPU tensors, e.g. backend='cpu:gloo,cuda:b200')");
+    const char* inl = std::getenv("NBDIST_B200_INLINE_SYNC_OPS");
+    inline_sync_ops_ = !(inl && inl[0] == '0');
+  }
+
+  ~BackendB200() override {
+    try {
+      shutdown();
+    } catch (...) {
+    }
+  }
+
+  const std::string getBackendName() const override { return kBackendName; }
+
+  void setTimeout(std::chrono::milliseconds timeout) override {
+    timeout_ = timeout;
+    if (comm_) nbd_comm_set_timeout_ms(comm_, (uint64_t)timeout.count());
+  }
+
+  void abort() override {
+    std::lock_guard<std::mutex> lk(mu_);
+    if (comm_) nbd_comm_abort(comm_);
+  }
+
+  // Teardown never blocks on peers for long: a bounded store handshake (so that
+  // nobody unmaps an arena a slow peer is still pulling from), then free.
+  void shutdown() override {
+    std::lock_guard<std::mutex> lk(mu_);
+    if (!comm_) return;
+    {
+      c10::cuda::CUDAGuard g(device_);
+      if (comm_stream_) cudaStreamSynchronize(comm_stream_->stream());
+      cudaStreamSynchronize(c10::cuda::getCurrentCUDAStream(device_));
+    }
+    if (getSize() > 1) {
+      try {
+        const std::string key = "nbd_b200/shutdown";
+        store_->add(key, 1);
+        const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(shutdown_wait_ms());
+        while (store_->add(key, 0) < getSize() && std::chrono::steady_clock::now() < deadline)
+          std::this_thread::sleep_for(std::chrono::milliseconds(5));
+      } catch (...) {
+        // store already gone (rank 0 exited or peers were killed): nothing to wait for
+      }
+    }
+    nbd_comm_destroy(comm_);
+    comm_ = nullptr;
+    comm_stream_.reset();
+  }
+
+  c10d::ErrorType getError() override {
+    if (!comm_) return c10d::ErrorType::SUCCESS;
+    const int rc = nbd_comm_async_error(comm_);
+    if (rc == NBD_OK) return c10d::ErrorType::SUCCESS;
+    return rc == NBD_ERR_TIMEOUT ? c10d::ErrorType::TIMEOUT : c10d::ErrorType::COMM_ERROR;
+  }
+
+  // ---- collectives ---------------------------------------------------------
+  c10::intrusive_ptr<c10d::Work> allreduce(std::vector<at::Tensor>& tensors,
+                                           const c10d::AllreduceOptions& opts) override {
+    TORCH_CHECK(tensors.size() == 1, "[b200] allreduce expects exactly one tensor");
+    auto& t = tensors[0];
+    check_tensor(t);
+    const int dtype = to_nbd_dtype(t.scalar_type(), true), op = to_nbd_op(opts.reduceOp);
+    return run(c10d::OpType::ALLREDUCE, "b200:all_reduce", t.get_device(), {t}, {t}, opts.asyncOp, false,
+               [&](cudaStream_t s) {
+                 return nbd_all_reduce(comm_, t.data_ptr(), t.data_ptr(), (size_t)t.numel(), dtype, op, s);
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> allreduce_coalesced(std::vector<at::Tensor>& tensors,
+                                                     const c10d::AllreduceCoalescedOptions& opts) override {
+    TORCH_CHECK(!tensors.empty(), "[b200] allreduce_coalesced needs at least one tensor");
+    for (auto& t : tensors) check_tensor(t);
+    const int op = to_nbd_op(opts.reduceOp);
+    return run(c10d::OpType::ALLREDUCE_COALESCED, "b200:all_reduce_coalesced", tensors[0].get_device(), tensors,
+               tensors, opts.asyncOp, false, [&](cudaStream_t s) {
+                 for (auto& t : tensors) {
+                   int rc = nbd_all_reduce(comm_, t.data_ptr(), t.data_ptr(), (size_t)t.numel(),
+                                           to_nbd_dtype(t.scalar_type(), true), op, s);
+                   if (rc != NBD_OK) return rc;
+                 }
+                 return (int)NBD_OK;
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> broadcast(std::vector<at::Tensor>& tensors,
+                                           const c10d::BroadcastOptions& opts) override {
+    TORCH_CHECK(tensors.size() == 1, "[b200] broadcast expects exactly one tensor");
+    auto& t = tensors[0];
+    check_tensor(t);
+    TORCH_CHECK(opts.rootRank >= 0 && opts.rootRank < getSize(), "[b200] invalid root rank ", opts.rootRank);
+    const int root = (int)opts.rootRank;
+    return run(c10d::OpType::BROADCAST, "b200:broadcast", t.get_device(), {t}, {t}, opts.asyncOp, false,
+               [&](cudaStream_t s) {
+                 return nbd_broadcast(comm_, t.data_ptr(), (size_t)t.nbytes(), NBD_BYTES, root, s);
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> _allgather_base(at::Tensor& out, at::Tensor& in,
+                                                 const c10d::AllgatherOptions& opts) override {
+    check_tensor(out);
+    check_tensor(in);
+    TORCH_CHECK(out.scalar_type() == in.scalar_type(), "[b200] all_gather: output and input dtypes differ");
+    TORCH_CHECK(out.numel() == in.numel() * getSize(), "[b200] all_gather: output must hold world_size * input elements");
+    return run(c10d::OpType::_ALLGATHER_BASE, "b200:all_gather_into_tensor", in.get_device(), {in}, {out},
+               opts.asyncOp, false, [&](cudaStream_t s) {
+                 return nbd_all_gather(comm_, in.data_ptr(), out.data_ptr(), (size_t)in.nbytes(), NBD_BYTES, s);
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> allgather(std::vector<std::vector<at::Tensor>>& outs, std::vector<at::Tensor>& ins,
+                                           const c10d::AllgatherOptions& opts) override {
+    TORCH_CHECK(ins.size() == 1 && outs.size() == 1, "[b200] allgather expects one input tensor and one output list");
+    auto& in = ins[0];
+    auto& list = outs[0];
+    check_tensor(in);
+    TORCH_CHECK((int)list.size() == getSize(), "[b200] all_gather: output list must have world_size tensors");
+    for (auto& o : list) {
+      check_tensor(o);
+      TORCH_CHECK(o.scalar_type() == in.scalar_type() && o.numel() == in.numel(),
+                  "[b200] all_gather: every output tensor must match the input's dtype and size");
+    }
+    std::vector<at::Tensor> all_out(list.begin(), list.end());
+    return run(c10d::OpType::ALLGATHER, "b200:all_gather", in.get_device(), {in}, all_out, opts.asyncOp, false,
+               [&](cudaStream_t s) {
+                 // gather into one flat buffer, then scatter to the caller's list on the same stream
+                 at::Tensor flat = at::empty({(int64_t)getSize() * in.numel()}, in.options());
+                 note_stream(flat);
+                 int rc = nbd_all_gather(comm_, in.data_ptr(), flat.data_ptr(), (size_t)in.nbytes(), NBD_BYTES, s);
+                 if (rc != NBD_OK) return rc;
+                 for (int r = 0; r < getSize(); ++r)
+                   list[r].copy_(flat.narrow(0, (int64_t)r * in.numel(), in.numel()).view_as(list[r]), true);
+                 return (int)NBD_OK;
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> allgather_into_tensor_coalesced(std::vector<at::Tensor>& outs,
+                                                                 std::vector<at::Tensor>& ins,
+                                                                 const c10d::AllgatherOptions& opts) override {
+    TORCH_CHECK(outs.size() == ins.size() && !ins.empty(), "[b200] all_gather coalesced: list sizes differ");
+    for (size_t i = 0; i < ins.size(); ++i) {
+      check_tensor(ins[i]);
+      check_tensor(outs[i]);
+      TORCH_CHECK(outs[i].numel() == ins[i].numel() * getSize() && outs[i].scalar_type() == ins[i].scalar_type(),
+                  "[b200] all_gather coalesced: bad output size/dtype at index ", i);
+    }
+    return run(c10d::OpType::COALESCED, "b200:all_gather_into_tensor_coalesced", ins[0].get_device(), ins, outs,
+               opts.asyncOp, false, [&](cudaStream_t s) {
+                 for (size_t i = 0; i < ins.size(); ++i) {
+                   int rc = nbd_all_gather(comm_, ins[i].data_ptr(), outs[i].data_ptr(), (size_t)ins[i].nbytes(),
+                                           NBD_BYTES, s);
+                   if (rc != NBD_OK) return rc;
+                 }
+                 return (int)NBD_OK;
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> _reduce_scatter_base(at::Tensor& out, at::Tensor& in,
+                                                      const c10d::ReduceScatterOptions& opts) override {
+    check_tensor(out);
+    check_tensor(in);
+    TORCH_CHECK(out.scalar_type() == in.scalar_type(), "[b200] reduce_scatter: output and input dtypes differ");
+    TORCH_CHECK(in.numel() == out.numel() * getSize(), "[b200] reduce_scatter: input must hold world_size * output elements");
+    const int dtype = to_nbd_dtype(in.scalar_type(), true), op = to_nbd_op(opts.reduceOp);
+    return run(c10d::OpType::_REDUCE_SCATTER_BASE, "b200:reduce_scatter_tensor", in.get_device(), {in}, {out},
+               opts.asyncOp, false, [&](cudaStream_t s) {
+                 return nbd_reduce_scatter(comm_, in.data_ptr(), out.data_ptr(), (size_t)out.numel(), dtype, op, s);
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> reduce_scatter(std::vector<at::Tensor>& outs,
+                                                std::vector<std::vector<at::Tensor>>& ins,
+                                                const c10d::ReduceScatterOptions& opts) override {
+    TORCH_CHECK(outs.size() == 1 && ins.size() == 1, "[b200] reduce_scatter expects one output tensor and one input list");
+    auto& out = outs[0];
+    auto& list = ins[0];
+    check_tensor(out);
+    TORCH_CHECK((int)list.size() == getSize(), "[b200] reduce_scatter: input list must have world_size tensors");
+    for (auto& t : list) {
+      check_tensor(t);
+      TORCH_CHECK(t.scalar_type() == out.scalar_type() && t.numel() == out.numel(),
+                  "[b200] reduce_scatter: every input tensor must match the output's dtype and size");
+    }
+    const int dtype = to_nbd_dtype(out.scalar_type(), true), op = to_nbd_op(opts.reduceOp);
+    std::vector<at::Tensor> all_in(list.begin(), list.end());
+    return run(c10d::OpType::REDUCE_SCATTER, "b200:reduce_scatter", out.get_device(), all_in, {out}, opts.asyncOp,
+               false, [&](cudaStream_t s) {
+                 std::vector<at::Tensor> flat_parts;
+                 flat_parts.reserve(list.size());
+                 for (auto& t : list) flat_parts.push_back(t.reshape({-1}));
+                 at::Tensor flat = at::cat(flat_parts, 0);
+                 note_stream(flat);
+                 return nbd_reduce_scatter(comm_, flat.data_ptr(), out.data_ptr(), (size_t)out.numel(), dtype, op, s);
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> reduce_scatter_tensor_coalesced(std::vector<at::Tensor>& outs,
+                                                                 std::vector<at::Tensor>& ins,
+                                                                 const c10d::ReduceScatterOptions& opts) override {
+    TORCH_CHECK(outs.size() == ins.size() && !ins.empty(), "[b200] reduce_scatter coalesced: list sizes differ");
+    for (size_t i = 0; i < ins.size(); ++i) {
+      check_tensor(ins[i]);
+      check_tensor(outs[i]);
+      TORCH_CHECK(ins[i].numel() == outs[i].numel() * getSize() && outs[i].scalar_type() == ins[i].scalar_type(),
+                  "[b200] reduce_scatter coalesced: bad input size/dtype at index ", i);
+    }
+    const int op = to_nbd_op(opts.reduceOp);
+    return run(c10d::OpType::COALESCED, "b200:reduce_scatter_tensor_coalesced", ins[0].get_device(), ins, outs,
+               opts.asyncOp, false, [&](cudaStream_t s) {
+                 for (size_t i = 0; i < ins.size(); ++i) {
+                   int rc = nbd_reduce_scatter(comm_, ins[i].data_ptr(), outs[i].data_ptr(), (size_t)outs[i].numel(),
+                                               to_nbd_dtype(ins[i].scalar_type(), true), op, s);
+                   if (rc != NBD_OK) return rc;
+                 }
+                 return (int)NBD_OK;
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> barrier(const c10d::BarrierOptions& opts) override {
+    c10::DeviceIndex dev = device_;
+    if (!comm_) {
+      if (opts.device.has_value() && opts.device->has_index()) dev = opts.device->index();
+      else if (!opts.device_ids.empty()) dev = (c10::DeviceIndex)opts.device_ids[0];
+      else if (getBoundDeviceId().has_value()) dev = getBoundDeviceId()->index();
+      else dev = c10::cuda::current_device();
+    }
+    return run(c10d::OpType::BARRIER, "b200:barrier", dev, {}, {}, opts.asyncOp, true,
+               [&](cudaStream_t s) { return nbd_barrier(comm_, s); });
+  }
+
+  // ---- extras exposed to Python ------------------------------------------------
+  void set_tunable(const std::string& name, uint64_t value) {
+    tunables_.emplace_back(name, value);
+    if (comm_) NBD_CHECK(nbd_comm_set_tunable(comm_, name.c_str(), value), "set_tunable");
+  }
+  std::string last_algo() { return comm_ ? nbd_last_algo(comm_) : "none"; }
+  int64_t device_index() const { return comm_ ? (int64_t)device_ : -1; }
+  void set_inline_sync_ops(bool v) { inline_sync_ops_ = v; }
+
+ private:
+  static int64_t shutdown_wait_ms() {
+    const char* e = std::getenv("NBDIST_B200_SHUTDOWN_WAIT_MS");
+    return e ? std::atoll(e) : 2000;
+  }
+
+  // First collective binds the communicator to the tensor's device (not to the
+  // rank: worker.py sets LOCAL_RANK=rank regardless of --gpu-ids)
+  // and exchanges CUDA-IPC handles over the store torch created at
+  // ref:src/nbdistributed/worker.py:151.
+  void ensure_comm(c10::DeviceIndex dev) {
+    if (comm_) {
+      TORCH_CHECK(dev == device_, "[b200] this process group is bound to cuda:", (int)device_, " but got a tensor on cuda:",
+                  (int)dev, " (one GPU per rank)");
+      return;
+    }
+    device_ = dev;
+    c10::cuda::CUDAGuard g(dev);
+    size_t stage = 0;
+    NBD_CHECK(nbd_comm_create(&comm_, getRank(), getSize(), (int)dev, stage), "nbd_comm_create");
+    nbd_comm_set_timeout_ms(comm_, (uint64_t)timeout_.count());
+    for (auto& kv : tunables_) nbd_comm_set_tunable(comm_, kv.first.c_str(), kv.second);
+    if (getSize() > 1) {
+      std::vector<uint8_t> mine(NBD_HANDLE_BYTES);
+      NBD_CHECK(nbd_comm_get_handle(comm_, mine.data()), "nbd_comm_get_handle");
+      store_->set(c10::str("nbd_b200/handle/", getRank()), mine);
+      std::vector<uint8_t> all((size_t)getSize() * NBD_HANDLE_BYTES);
+      for (int r = 0; r < getSize(); ++r) {
+        std::vector<uint8_t> h = (r == getRank()) ? mine : store_->get(c10::str("nbd_b200/handle/", r));
+        TORCH_CHECK(h.size() == NBD_HANDLE_BYTES, "[b200] malformed IPC handle from rank ", r);
+        std::memcpy(all.data() + (size_t)r * NBD_HANDLE_BYTES, h.data(), NBD_HANDLE_BYTES);
+      }
+      int rc = nbd_comm_connect(comm_, all.data());
+      if (rc != NBD_OK) {
+        nbd_comm_destroy(comm_);
+        comm_ = nullptr;
+        throw_nbd(rc, "nbd_comm_connect");
+      }
+    }
+    comm_stream_ = c10::cuda::getStreamFromPool(/*isHighPriority=*/true, dev);
+  }
+
+  // temporaries created inside an enqueue lambda are used on cur_stream_
+  void note_stream(const at::Tensor& t) {
+    if (cur_stream_ && *cur_stream_ != c10::cuda::getCurrentCUDAStream(device_))
+      c10::cuda::CUDACachingAllocator::recordStream(t.storage().data_ptr(), *cur_stream_);
+  }
+
+  template <typename F>
+  c10::intrusive_ptr<c10d::Work> run(c10d::OpType type, const char* title, c10::DeviceIndex dev,
+                                     std::vector<at::Tensor> inputs, std::vector<at::Tensor> outputs, bool async_op,
+                                     bool is_barrier, F&& enqueue) {
+    std::lock_guard<std::mutex> lk(mu_);
+    ensure_comm(dev);
+    c10::cuda::CUDAGuard g(dev);
+    auto caller = c10::cuda::getCurrentCUDAStream(dev);
+    // Synchronous calls (dist.all_reduce(x) from a cell: async_op=False, wait() follows
+    // immediately) run in line on the caller's stream: same semantics, no event round trip.
+    // Asynchronous calls (DDP buckets) run on the backend's stream so they overlap compute.
+    const bool inline_op = inline_sync_ops_ && !async_op;
+    c10::cuda::CUDAStream stream = inline_op ? caller : *comm_stream_;
+    if (!inline_op) {
+      at::cuda::CUDAEvent ready;
+      ready.record(caller);
+      ready.block(stream);
+      for (auto& t : inputs) c10::cuda::CUDACachingAllocator::recordStream(t.storage().data_ptr(), stream);
+      for (auto& t : outputs) c10::cuda::CUDACachingAllocator::recordStream(t.storage().data_ptr(), stream);
+    }
+    // collectives of one communicator share its staging arena and flags: never let two
+    // of them overlap, whichever streams they were issued on
+    if (has_last_ && last_stream_ != stream) last_done_.block(stream);
+    int rc;
+    {
+      c10::cuda::CUDAStreamGuard sg(stream);
+      cur_stream_ = stream;
+      rc = enqueue(stream.stream());
+      cur_stream_.reset();
+    }
+    if (rc != NBD_OK) throw_nbd(rc, title);
+    auto work = c10::make_intrusive<WorkB200>(getRank(), type, title, dev, comm_, std::move(outputs), is_barrier);
+    work->mark_enqueued(stream);
+    last_done_.record(stream);
+    last_stream_ = stream;
+    has_last_ = true;
+    return work;
+  }
+
+  c10::intrusive_ptr<c10d::Store> store_;
+  std::chrono::milliseconds timeout_;
+  std::mutex mu_;
+  nbd_comm_t comm_ = nullptr;
+  c10::DeviceIndex device_ = -1;
+  std::optional<c10::cuda::CUDAStream> comm_stream_;
+  std::optional<c10::cuda::CUDAStream> cur_stream_;
+  at::cuda::CUDAEvent last_done_;
+  c10::cuda::CUDAStream last_stream_ = c10::cuda::getDefaultCUDAStream();
+  bool has_last_ = false;
+  bool inline_sync_ops_ = true;
+  std::vector<std::pair<std::string, uint64_t>> tunables_;
+};
+
+c10::intrusive_ptr<c10d::Backend> create_backend(const c10::intrusive_ptr<c10d::Store>& store, int rank, int size,
+                                                 const std::chrono::duration<float>& timeout) {
+  return c10::make_intrusive<BackendB200>(store, rank, size,
+                                          std::chrono::duration_cast<std::chrono::milliseconds>(timeout));
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.doc() = "c10d backend 'b200': NVLink/NVSwitch P2P collectives for one B200 node";
+  py::class_<BackendB200, c10::intrusive_ptr<BackendB200>, c10d::Backend>(m, "BackendB200")
+      .def("set_tunable", &BackendB200::set_tunable)
+      .def("last_algo", &BackendB200::last_algo)
+      .def("device_index", &BackendB200::device_index)
+      .def("set_inline_sync_ops", &BackendB200::set_inline_sync_ops);
+  m.def("create_backend", &create_backend, py::arg("store"), py::arg("rank"), py::arg("size"), py::arg("timeout"),
+        "creator for torch.distributed.Backend.register_backend");
+  m.def("launch_count", []() { return nbd_launch_count(); });
+  m.def("nbd_version", []() { return nbd_version(); });
+}

@@ -54,6 +54,8 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
     if not force and _newer(LIB, deps):
         return LIB
     cmd = [_nvcc(), *NVCC_ARCH, "-lineinfo", "-O3", "-std=c++17", "-shared", "-Xcompiler", "-fPIC",
+           # keep the statically linked CUDA runtime private to this library
+           "-Xlinker", "--exclude-libs,ALL",
            "-I", os.path.join(ROOT, "include"), "-o", LIB, *cu]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
@@ -68,21 +70,30 @@ def build_c10d(force: bool = False, verbose: bool = False) -> str:
     deps = [src, os.path.join(ROOT, "include", "nbdist_b200.h")]
     if not force and _newer(C10D, deps):
         return C10D
+    build_lib()
     import torch
     from torch.utils import cpp_extension as ce
 
     torch_lib = os.path.join(os.path.dirname(torch.__file__), "lib")
     inc = [*ce.include_paths(device_type="cuda"), sysconfig.get_paths()["include"], os.path.join(ROOT, "include")]
-    cxx = os.environ.get("CXX", "g++")
-    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden",
+    # The distro g++ first: this image's $CXX wrapper (/opt/gcc) resolves -lstdc++ to a static
+    # libstdc++.a, and a private second copy of libstdc++ inside a torch extension crashes in
+    # iostream/locale code (c10::str) as soon as objects cross the two copies.
+    cxx = next((c for c in ("/usr/bin/g++", os.environ.get("CXX"), shutil.which("g++")) if c and os.path.exists(c)))
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", "-Wno-interference-size",
            "-DTORCH_EXTENSION_NAME=_c10d_b200", "-DTORCH_API_INCLUDE_EXTENSION_H",
            f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}",
            *[f"-I{p}" for p in inc], src, "-o", C10D,
            f"-L{torch_lib}", f"-Wl,-rpath,{torch_lib}",
-           "-ltorch_python", "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-lc10", "-lc10_cuda", "-ldl"]
+           "-ltorch_python", "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-lc10", "-lc10_cuda",
+           f"-L{HERE}", "-l:libnbdist_b200.so", "-Wl,-rpath,$ORIGIN", "-ldl"]
     if verbose:
         print(" ".join(cmd), file=sys.stderr)
     subprocess.run(cmd, check=True)
+    syms = subprocess.run(["nm", "-C", "--defined-only", C10D], capture_output=True, text=True).stdout
+    if " T std::locale::" in syms:
+        os.remove(C10D)
+        raise RuntimeError(f"{cxx} linked libstdc++ statically into {C10D}; use the distro g++")
     return C10D
 
 

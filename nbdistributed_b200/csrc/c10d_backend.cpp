@@ -21,7 +21,14 @@
 #include <torch/csrc/distributed/c10d/Work.hpp>
 #include <torch/extension.h>
 
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
+
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <thread>
 
@@ -30,6 +37,29 @@
 namespace {
 
 constexpr const char* kBackendName = "b200";
+
+bool debug_on() {
+  static const bool on = [] { const char* e = std::getenv("NBDIST_B200_DEBUG"); return e && e[0] != '0'; }();
+  return on;
+}
+#define NBD_DBG(...)                                 \
+  do {                                               \
+    if (debug_on()) {                                \
+      std::fprintf(stderr, "[b200 glue] " __VA_ARGS__); \
+      std::fprintf(stderr, "\n");                    \
+      std::fflush(stderr);                           \
+    }                                                \
+  } while (0)
+
+void segv_backtrace(int sig) {
+  void* frames[64];
+  const int n = backtrace(frames, 64);
+  const char msg[] = "[b200 glue] fatal signal, native backtrace:\n";
+  (void)!write(2, msg, sizeof(msg) - 1);
+  backtrace_symbols_fd(frames, n, 2);
+  signal(sig, SIG_DFL);
+  raise(sig);
+}
 
 [[noreturn]] void throw_nbd(int rc, const char* what) {
   std::string msg = c10::str("[", kBackendName, "] ", what, ": ", nbd_error_string(rc));
@@ -138,6 +168,7 @@ class BackendB200 : public c10d::Backend {
                 "NVLink/NVSwitch node of at most ", NBD_MAX_RANKS, " GPUs");
     TORCH_CHECK(at::cuda::is_available(), "[b200] no CUDA device: the b200 backend has no CPU fallback "
                 "(use 'gloo' for CPU tensors, e.g. backend='cpu:gloo,cuda:b200')");
+    if (debug_on()) signal(SIGSEGV, segv_backtrace);
     const char* inl = std::getenv("NBDIST_B200_INLINE_SYNC_OPS");
     inline_sync_ops_ = !(inl && inl[0] == '0');
   }
@@ -396,20 +427,25 @@ class BackendB200 : public c10d::Backend {
     device_ = dev;
     c10::cuda::CUDAGuard g(dev);
     size_t stage = 0;
+    NBD_DBG("rank %d: creating communicator on cuda:%d", getRank(), (int)dev);
     NBD_CHECK(nbd_comm_create(&comm_, getRank(), getSize(), (int)dev, stage), "nbd_comm_create");
     nbd_comm_set_timeout_ms(comm_, (uint64_t)timeout_.count());
     for (auto& kv : tunables_) nbd_comm_set_tunable(comm_, kv.first.c_str(), kv.second);
     if (getSize() > 1) {
       std::vector<uint8_t> mine(NBD_HANDLE_BYTES);
       NBD_CHECK(nbd_comm_get_handle(comm_, mine.data()), "nbd_comm_get_handle");
+      NBD_DBG("rank %d: publishing IPC handle", getRank());
       store_->set(c10::str("nbd_b200/handle/", getRank()), mine);
+      NBD_DBG("rank %d: published", getRank());
       std::vector<uint8_t> all((size_t)getSize() * NBD_HANDLE_BYTES);
       for (int r = 0; r < getSize(); ++r) {
         std::vector<uint8_t> h = (r == getRank()) ? mine : store_->get(c10::str("nbd_b200/handle/", r));
         TORCH_CHECK(h.size() == NBD_HANDLE_BYTES, "[b200] malformed IPC handle from rank ", r);
         std::memcpy(all.data() + (size_t)r * NBD_HANDLE_BYTES, h.data(), NBD_HANDLE_BYTES);
       }
+      NBD_DBG("rank %d: got all handles, connecting", getRank());
       int rc = nbd_comm_connect(comm_, all.data());
+      NBD_DBG("rank %d: connect rc=%d", getRank(), rc);
       if (rc != NBD_OK) {
         nbd_comm_destroy(comm_);
         comm_ = nullptr;
@@ -447,12 +483,14 @@ class BackendB200 : public c10d::Backend {
     }
     // collectives of one communicator share its staging arena and flags: never let two
     // of them overlap, whichever streams they were issued on
-    if (has_last_ && last_stream_ != stream) last_done_.block(stream);
+    if (has_last_ && *last_stream_ != stream) last_done_.block(stream);
     int rc;
     {
       c10::cuda::CUDAStreamGuard sg(stream);
       cur_stream_ = stream;
+      NBD_DBG("rank %d: enqueue %s (inline=%d)", getRank(), title, (int)inline_op);
       rc = enqueue(stream.stream());
+      NBD_DBG("rank %d: enqueue %s rc=%d", getRank(), title, rc);
       cur_stream_.reset();
     }
     if (rc != NBD_OK) throw_nbd(rc, title);
@@ -472,7 +510,7 @@ class BackendB200 : public c10d::Backend {
   std::optional<c10::cuda::CUDAStream> comm_stream_;
   std::optional<c10::cuda::CUDAStream> cur_stream_;
   at::cuda::CUDAEvent last_done_;
-  c10::cuda::CUDAStream last_stream_ = c10::cuda::getDefaultCUDAStream();
+  std::optional<c10::cuda::CUDAStream> last_stream_;
   bool has_last_ = false;
   bool inline_sync_ops_ = true;
   std::vector<std::pair<std::string, uint64_t>> tunables_;
@@ -495,6 +533,15 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("set_inline_sync_ops", &BackendB200::set_inline_sync_ops);
   m.def("create_backend", &create_backend, py::arg("store"), py::arg("rank"), py::arg("size"), py::arg("timeout"),
         "creator for torch.distributed.Backend.register_backend");
+  m.def("store_roundtrip", [](const c10::intrusive_ptr<c10d::Store>& store, const std::string& key, int nbytes) {
+    // the same set/get sequence ensure_comm() uses for the IPC handles; lets the CPU test
+    // suite exercise the store leg of the boundary without a GPU
+    std::vector<uint8_t> v((size_t)nbytes);
+    for (int i = 0; i < nbytes; ++i) v[(size_t)i] = (uint8_t)(i * 7 + 1);
+    store->set(key, v);
+    std::vector<uint8_t> back = store->get(key);
+    return back == v;
+  }, py::call_guard<py::gil_scoped_release>());
   m.def("launch_count", []() { return nbd_launch_count(); });
   m.def("nbd_version", []() { return nbd_version(); });
 }

@@ -259,10 +259,12 @@ __device__ __forceinline__ void region_st(const Region& r, bool aligned, u64 i, 
   }
 }
 
-// CTA b of nb owns units [lo, hi) of a span of `units` units.
-__device__ __forceinline__ void block_span(u64 units, u64& lo, u64& hi) {
+// CTA b of nb owns units [lo, hi) of a span.  The cut is made on `full_units` (the span
+// of a full-size chunk) and clipped to `units` (this chunk), so that a CTA touches the same
+// staging offsets in every chunk: the flag barriers only order same-index CTAs.
+__device__ __forceinline__ void block_span(u64 full_units, u64 units, u64& lo, u64& hi) {
   const u64 nb = gridDim.x;
-  u64 per = (units + nb - 1) / nb;
+  u64 per = (full_units + nb - 1) / nb;
   per = (per + kThreads - 1) / kThreads * kThreads;
   lo = (u64)blockIdx.x * per;
   if (lo > units) lo = units;

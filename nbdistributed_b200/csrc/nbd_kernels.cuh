@@ -14,7 +14,10 @@
 //
 // Staging-half reuse is safe because a rank signals barrier(c) only after it
 // finished every access of step c-1, and nobody touches half (c+1)%2 for step
-// c+1 before it has waited on barrier(c).  See DESIGN.md "Flag protocol".
+// c+1 before it has waited on barrier(c).  Barriers are per CTA index, so CTA b
+// must own the SAME staging offsets in every chunk of a launch: spans are cut
+// from the full chunk size and merely clipped for a ragged last chunk.
+// See DESIGN.md "Flag protocol".
 #pragma once
 
 #include "nbd_device.cuh"
@@ -78,7 +81,7 @@ k_allreduce_oneshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
     const Region src = make_region(ub.send + off, cb);
     u64 lo, hi;
-    block_span(units_of(cb), lo, hi);
+    block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     const bool al = region_aligned(src);
     // one read of the user chunk, N-1 remote writes, peers interleaved
@@ -112,7 +115,7 @@ k_allreduce_oneshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 off = (u64)cidx * op.chunk_bytes;
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
     u64 lo, hi;
-    block_span(units_of(cb), lo, hi);
+    block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     reduce_units<T, SUM, false>(c, make_region(ub.send + off, cb), c.stage[r] + half, slot_stride,
                                 make_region(ub.recv + off, cb), nullptr, lo, hi, op.op, op.avg);
@@ -144,7 +147,7 @@ k_allreduce_twoshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 su = shard_units(cb);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     u64 lo, hi;
-    block_span(su, lo, hi);
+    block_span(shard_units(op.chunk_bytes), su, lo, hi);
 #pragma unroll 1
     for (u64 base = lo; base < hi; base += 4ull * kThreads) {
       const u64 bhi = (base + 4ull * kThreads < hi) ? base + 4ull * kThreads : hi;
@@ -171,7 +174,7 @@ k_allreduce_twoshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 su = shard_units(cb);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     u64 lo, hi;
-    block_span(su, lo, hi);
+    block_span(shard_units(op.chunk_bytes), su, lo, hi);
     {
       const u64 sb = clip_bytes(cb, (u64)r * su * kUnit, su * kUnit);
       const u64 ru = units_of(sb);
@@ -218,7 +221,7 @@ k_reduce_scatter(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     u64 lo, hi;
-    block_span(units_of(cb), lo, hi);
+    block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
 #pragma unroll 1
     for (u64 base = lo; base < hi; base += 4ull * kThreads) {
       const u64 bhi = (base + 4ull * kThreads < hi) ? base + 4ull * kThreads : hi;
@@ -240,7 +243,7 @@ k_reduce_scatter(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     u64 lo, hi;
-    block_span(units_of(cb), lo, hi);
+    block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
     reduce_units<T, SUM, false>(c, make_region(ub.send + (u64)r * op.bytes + off, cb), c.stage[r] + half,
                                 slot_stride, make_region(ub.recv + off, cb), nullptr, lo, hi, op.op, op.avg);
   }
@@ -265,7 +268,7 @@ k_all_gather(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     u64 lo, hi;
-    block_span(units_of(cb), lo, hi);
+    block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
     copy_region_to_stage<4>(c.stage[r] + half, make_region(ub.send + off, cb), lo, hi);
   };
 
@@ -277,7 +280,7 @@ k_all_gather(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     u64 lo, hi;
-    block_span(units_of(cb), lo, hi);
+    block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
 #pragma unroll 1
     for (u64 base = lo; base < hi; base += 4ull * kThreads) {
       const u64 bhi = (base + 4ull * kThreads < hi) ? base + 4ull * kThreads : hi;
@@ -325,7 +328,7 @@ k_broadcast(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
       const Region src = make_region(ub.recv + off, cb);
       const bool al = region_aligned(src);
       u64 lo, hi;
-      block_span(units_of(cb), lo, hi);
+      block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
       for (u64 base = lo + threadIdx.x; base < hi; base += 2ull * kThreads) {
         uint4 v[2];
 #pragma unroll
@@ -350,7 +353,7 @@ k_broadcast(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     } else {
       const u64 su = shard_units(cb);
       u64 lo, hi;
-      block_span(su, lo, hi);
+      block_span(shard_units(op.chunk_bytes), su, lo, hi);
 #pragma unroll 1
       for (u64 base = lo; base < hi; base += 4ull * kThreads) {
         const u64 bhi = (base + 4ull * kThreads < hi) ? base + 4ull * kThreads : hi;
@@ -380,12 +383,12 @@ k_broadcast(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     if (op.algo == 0) {
       u64 lo, hi;
-      block_span(units_of(cb), lo, hi);
+      block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
       copy_stage_to_region<4>(make_region(ub.recv + off, cb), c.stage[r] + half, lo, hi);
     } else {
       const u64 su = shard_units(cb);
       u64 lo, hi;
-      block_span(su, lo, hi);
+      block_span(shard_units(op.chunk_bytes), su, lo, hi);
 #pragma unroll 1
       for (u64 base = lo; base < hi; base += 4ull * kThreads) {
         const u64 bhi = (base + 4ull * kThreads < hi) ? base + 4ull * kThreads : hi;

@@ -439,6 +439,14 @@ static int pick_blocks(const nbd_comm* c, u64 units_per_block_span, int emu_worl
   return (int)(want < cap ? want : cap);
 }
 
+// A message that fits one chunk gets a chunk of exactly its (aligned) size: CTA spans are
+// cut from chunk_bytes (see block_span), so an oversized chunk would idle most CTAs.
+static inline u64 fit_chunk(u64 chunk, u64 bytes, u64 align) {
+  if (bytes >= chunk) return chunk;
+  const u64 fit = ceil_div(bytes, align) * align;
+  return fit < chunk ? fit : chunk;
+}
+
 static const u64 kDefChunkAR = 32ull << 20;    // message bytes per step
 static const u64 kDefChunkShard = 8ull << 20;  // shard bytes per step (rs / ag)
 static const u64 kDefChunkBcast = 32ull << 20;
@@ -459,9 +467,10 @@ static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
     u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkAR / N;
     if (chunk < kUnit) chunk = kUnit;
     if (chunk > cap) chunk = cap;
+    chunk = fit_chunk(chunk, bytes, kUnit);
     p.op.chunk_bytes = chunk;
     p.op.nchunks = (u32)ceil_div(bytes, chunk);
-    p.nblocks = pick_blocks(c, ceil_div(bytes < chunk ? bytes : chunk, kUnit), emu_world);
+    p.nblocks = pick_blocks(c, ceil_div(chunk, kUnit), emu_world);
     c->last_algo = "ar_oneshot";
   } else {
     p.op.algo = 2;
@@ -470,9 +479,10 @@ static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
     u64 chunk = c->t_chunk ? floor_to(c->t_chunk, (u64)kUnit * N) : kDefChunkAR;
     if (chunk < (u64)kUnit * N) chunk = (u64)kUnit * N;
     if (chunk > cap) chunk = cap;
+    chunk = fit_chunk(chunk, bytes, (u64)kUnit * N);
     p.op.chunk_bytes = chunk;
     p.op.nchunks = (u32)ceil_div(bytes, chunk);
-    p.nblocks = pick_blocks(c, ceil_div(ceil_div(bytes < chunk ? bytes : chunk, kUnit), N), emu_world);
+    p.nblocks = pick_blocks(c, ceil_div(ceil_div(chunk, kUnit), N), emu_world);
     c->last_algo = "ar_twoshot";
   }
   return p;
@@ -491,9 +501,10 @@ static Plan plan_reduce_scatter(nbd_comm* c, u64 shard_bytes, int op, int emu_wo
   u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkShard;
   if (chunk < kUnit) chunk = kUnit;
   if (chunk > cap) chunk = cap;
+  chunk = fit_chunk(chunk, shard_bytes, kUnit);
   p.op.chunk_bytes = chunk;
   p.op.nchunks = (u32)ceil_div(shard_bytes, chunk);
-  p.nblocks = pick_blocks(c, ceil_div(shard_bytes < chunk ? shard_bytes : chunk, kUnit), emu_world);
+  p.nblocks = pick_blocks(c, ceil_div(chunk, kUnit), emu_world);
   c->last_algo = "reduce_scatter_push";
   return p;
 }
@@ -508,9 +519,10 @@ static Plan plan_all_gather(nbd_comm* c, u64 shard_bytes, int emu_world) {
   u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkShard;
   if (chunk < kUnit) chunk = kUnit;
   if (chunk > cap) chunk = cap;
+  chunk = fit_chunk(chunk, shard_bytes, kUnit);
   p.op.chunk_bytes = chunk;
   p.op.nchunks = (u32)ceil_div(shard_bytes, chunk);
-  p.nblocks = pick_blocks(c, ceil_div(shard_bytes < chunk ? shard_bytes : chunk, kUnit), emu_world);
+  p.nblocks = pick_blocks(c, ceil_div(chunk, kUnit), emu_world);
   c->last_algo = "all_gather_pull";
   return p;
 }
@@ -530,9 +542,10 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
     u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkBcast;
     if (chunk < kUnit) chunk = kUnit;
     if (chunk > cap) chunk = cap;
+    chunk = fit_chunk(chunk, bytes, kUnit);
     p.op.chunk_bytes = chunk;
     p.op.nchunks = (u32)ceil_div(bytes, chunk);
-    p.nblocks = pick_blocks(c, ceil_div(bytes < chunk ? bytes : chunk, kUnit), emu_world);
+    p.nblocks = pick_blocks(c, ceil_div(chunk, kUnit), emu_world);
     c->last_algo = "bcast_direct";
   } else {
     p.op.algo = 1;
@@ -541,9 +554,10 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
     u64 chunk = c->t_chunk ? floor_to(c->t_chunk, (u64)kUnit * nsh) : floor_to(kDefChunkBcast, (u64)kUnit * nsh);
     if (chunk < (u64)kUnit * nsh) chunk = (u64)kUnit * nsh;
     if (chunk > cap) chunk = cap;
+    chunk = fit_chunk(chunk, bytes, (u64)kUnit * nsh);
     p.op.chunk_bytes = chunk;
     p.op.nchunks = (u32)ceil_div(bytes, chunk);
-    p.nblocks = pick_blocks(c, ceil_div(ceil_div(bytes < chunk ? bytes : chunk, kUnit), nsh), emu_world);
+    p.nblocks = pick_blocks(c, ceil_div(ceil_div(chunk, kUnit), nsh), emu_world);
     c->last_algo = "bcast_scatter";
   }
   return p;

@@ -1,0 +1,183 @@
+"""Per-rank body of the multi-GPU backend tests (spawned by test_backend_multigpu.py, one
+process per GPU).  Every check compares the b200 backend (CUDA tensors) with the reference's
+CPU path — gloo, reached through the same process group because the backend string is
+"cpu:gloo,cuda:b200" — and with the numpy oracle, on identical seeded inputs."""
+from __future__ import annotations
+
+import os
+import sys
+import traceback
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from oracle import collectives_oracle as O  # noqa: E402
+from tests import helpers as H  # noqa: E402
+
+
+def _gather_cpu(dist, torch, x_cpu):
+    """All ranks' copies of a CPU tensor, through gloo."""
+    out = [torch.empty_like(x_cpu) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, x_cpu)
+    return out
+
+
+def _np(t, dtype):
+    return H.to_numpy(t, dtype)
+
+
+def body(rank: int, world: int, port: int) -> None:
+    import torch
+    import torch.distributed as dist
+
+    from nbdistributed_b200 import backend as B
+    from nbdistributed_b200 import worker_init as W
+
+    ns = W.init_worker(rank, world, "127.0.0.1", port, gpu_id=rank, backend="b200")
+    assert ns["__backend__"] == "cpu:gloo,cuda:b200"
+    assert ns["device"] == rank and ns["gpu_id"] == rank
+    dev = torch.device("cuda", rank)
+    be = B.get_backend()
+    assert type(be).__name__ == "BackendB200", type(be)
+
+    # ---- config 1: README example (ref:README.md:99-125) through the cell runner -------
+    W.run_cell(ns, "torch.manual_seed(1234 + rank)\nx = torch.randn(100, 100)\nxc = x.clone()\nxg = x.cuda()\n"
+                   "dist.all_reduce(xg)\ndist.all_reduce(xc)\n")
+    xg, xc = ns["xg"], ns["xc"]
+    allx = _gather_cpu(dist, torch, ns["x"])
+    want = O.reduce_rank_order([_np(a, "f32") for a in allx], "f32")
+    H.assert_same(_np(xg, "f32"), want, "f32", "README all_reduce vs oracle")
+    if world == 2:
+        assert torch.equal(xg.cpu(), xc), "README all_reduce: not bit-identical with gloo at N=2"
+    else:
+        tol = O.float_sum_tolerance([_np(a, "f32") for a in allx], "f32")
+        assert (np.abs(_np(xg, "f32").astype(np.float64) - _np(xc, "f32")) <= tol).all()
+    W.run_cell(ns, "torch.manual_seed(rank)\nmodel = torch.nn.Linear(10, 10).cuda()\n"
+                   "ref = [p.detach().cpu().clone() for p in model.parameters()]\n"
+                   "for param in model.parameters():\n    dist.broadcast(param.data, src=0)\n"
+                   "for p in ref:\n    dist.broadcast(p, src=0)\n")
+    for p, q in zip(ns["model"].parameters(), ns["ref"]):
+        assert torch.equal(p.detach().cpu(), q), "broadcast of Linear params differs from gloo"
+
+    # ---- all_reduce sweep: dtypes x sizes, bit-exact vs oracle (rank order) --------------
+    for dtype in ("f32", "bf16", "f16", "f64", "i32", "i64", "u8", "i8"):
+        for numel in (1, 127, 4096 + 5, (1 << 20) + 1, 3 << 20):
+            x = O.make_inputs(world, numel, dtype)
+            t = H.to_cuda(x[rank], dtype, dev)
+            dist.all_reduce(t)
+            H.assert_same(_np(t, dtype), O.reduce_rank_order(x, dtype), dtype,
+                          f"all_reduce {dtype} n={numel} algo={be.last_algo()}")
+    # integer all_reduce is bit-exact with gloo
+    x = O.make_inputs(world, 70001, "i64")
+    t = H.to_cuda(x[rank], "i64", dev)
+    c = torch.from_numpy(x[rank].copy())
+    dist.all_reduce(t)
+    dist.all_reduce(c)
+    assert torch.equal(t.cpu(), c)
+    # other ops
+    for dtype, op, dop in (("f32", "max", dist.ReduceOp.MAX), ("f32", "min", dist.ReduceOp.MIN),
+                           ("i32", "bxor", dist.ReduceOp.BXOR), ("bf16", "avg", dist.ReduceOp.AVG),
+                           ("f32", "prod", dist.ReduceOp.PRODUCT)):
+        x = O.make_inputs(world, 33333, dtype)
+        t = H.to_cuda(x[rank], dtype, dev)
+        dist.all_reduce(t, op=dop)
+        H.assert_same(_np(t, dtype), O.reduce_rank_order(x, dtype, op), dtype, f"all_reduce {op}")
+
+    # ---- broadcast: every root, latency and bandwidth paths, bit-exact -------------------
+    for nbytes in (40, 400, 12 * 1024 + 3, (1 << 20) + 17, (40 << 20) + 1):
+        for root in sorted({0, world - 1}):
+            x = O.make_inputs(world, nbytes, "u8", seed=7 + root)
+            t = H.to_cuda(x[rank], "u8", dev)
+            dist.broadcast(t, src=root)
+            H.assert_same(_np(t, "u8"), x[root], "u8", f"broadcast {nbytes}B root {root} algo={be.last_algo()}")
+
+    # ---- all_gather / reduce_scatter (tensor and list forms) -----------------------------
+    for dtype, numel in (("f32", 25), ("bf16", 4099), ("i64", 1 << 16), ("bf16", (2 << 20) + 8)):
+        x = O.make_inputs(world, numel, dtype)
+        t = H.to_cuda(x[rank], dtype, dev)
+        out = torch.empty(world * numel, dtype=t.dtype, device=dev)
+        dist.all_gather_into_tensor(out, t)
+        H.assert_same(_np(out, dtype), O.all_gather(x)[0], dtype, f"all_gather_into_tensor {dtype} {numel}")
+        lst = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(lst, t)
+        for r in range(world):
+            H.assert_same(_np(lst[r], dtype), x[r], dtype, f"all_gather list slot {r}")
+        xs = O.make_inputs(world, world * numel, dtype, seed=99)
+        s = H.to_cuda(xs[rank], dtype, dev)
+        o = torch.empty(numel, dtype=s.dtype, device=dev)
+        dist.reduce_scatter_tensor(o, s)
+        H.assert_same(_np(o, dtype), O.reduce_scatter(xs, dtype)[rank], dtype, f"reduce_scatter_tensor {dtype} {numel}")
+        o2 = torch.empty(numel, dtype=s.dtype, device=dev)
+        dist.reduce_scatter(o2, list(s.chunk(world)))
+        assert torch.equal(o, o2), "reduce_scatter list form differs from tensor form"
+
+    # ---- async ops, futures, barrier, non-contiguous rejection -----------------------------
+    x = O.make_inputs(world, 1 << 20, "f32", seed=3)
+    t = H.to_cuda(x[rank], "f32", dev)
+    work = dist.all_reduce(t, async_op=True)
+    work.wait()
+    H.assert_same(_np(t, "f32"), O.reduce_rank_order(x, "f32"), "f32", "async all_reduce")
+    t2 = H.to_cuda(x[rank], "f32", dev)
+    fut = dist.all_reduce(t2, async_op=True).get_future()
+    fut.wait()
+    assert torch.equal(fut.value()[0], t), "future value differs"
+    dist.barrier()
+    dist.barrier(device_ids=[rank])
+    try:
+        dist.all_reduce(torch.zeros(8, 8, device=dev).t())
+        raise AssertionError("non-contiguous tensor was accepted")
+    except ValueError:
+        pass
+    try:
+        dist.all_reduce(torch.zeros(8, device=dev, dtype=torch.int32), op=dist.ReduceOp.AVG)
+        raise AssertionError("integer AVG was accepted")
+    except Exception as e:  # noqa: BLE001
+        assert "AVG" in str(e) or "unsupported" in str(e), e
+
+    # ---- DDP: gradient all_reduce through getFuture (config 4 pattern, tiny model) -------
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.ReLU(), torch.nn.Linear(128, 8)).to(dev)
+    ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank])
+    torch.manual_seed(100 + rank)
+    inp = torch.randn(16, 64, device=dev)
+    ddp(inp).square().mean().backward()
+    # reference: local grads of an un-wrapped copy, averaged over ranks through gloo
+    torch.manual_seed(0)
+    plain = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.ReLU(), torch.nn.Linear(128, 8)).to(dev)
+    plain(inp).square().mean().backward()
+    for p, q in zip(ddp.module.parameters(), plain.parameters()):
+        g = q.grad.detach().cpu()
+        dist.all_reduce(g)
+        g /= world
+        assert torch.allclose(p.grad.cpu(), g, rtol=1e-5, atol=1e-6), "DDP gradient mismatch"
+
+    # ---- BASELINE-size message through properties: 256 MiB fp32, integer-valued ----------
+    numel = 64 << 20
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    big = torch.randint(-1000, 1000, (numel,), generator=g, device=dev, dtype=torch.int32)
+    ref = big.clone()
+    dist.all_reduce(ref)  # int32: exact
+    bigf = big.to(torch.float32)
+    dist.all_reduce(bigf)
+    assert torch.equal(bigf, ref.to(torch.float32)), "256 MiB all_reduce: fp32 sum of small ints must be exact"
+    chk = bigf.view(torch.int32).sum(dtype=torch.int64).cpu()
+    allchk = _gather_cpu(dist, torch, chk.reshape(1))
+    assert all(int(a) == int(allchk[0]) for a in allchk), "ranks disagree bit-wise on a 256 MiB all_reduce"
+    del big, ref, bigf
+    torch.cuda.synchronize()
+    W.shutdown_worker()
+
+
+def main(rank: int, world: int, port: int) -> None:
+    import faulthandler
+
+    faulthandler.enable(all_threads=True)
+    try:
+        body(rank, world, port)
+    except Exception:
+        traceback.print_exc()
+        raise

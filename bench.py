@@ -1,0 +1,564 @@
+#!/usr/bin/env python
+"""bench.py — the headline benchmark of the b200 collective backend.
+
+Metric (BASELINE.json): all_reduce bus GB/s (nccl-tests convention) — plus a message-size
+sweep for all_reduce / broadcast and the small-message latency as extra keys.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+* N = 1 (plain ``python bench.py``): the 1-GPU row of SURVEY.md §8(d).  R = 8 ranks are
+  emulated on the one GPU by a single cooperative launch per collective (same kernels, flag
+  protocol and staging as the multi-process backend; "peers" are local buffers), so the
+  bound is local HBM.  A step = one fp32 SUM all_reduce of 256 MiB per rank.
+* N > 1 (under ``python -m torch.distributed.run --nproc-per-node N``): one process per
+  GPU through ``dist.all_reduce`` on backend "b200".  A step = the same 256 MiB all_reduce.
+  The bound is NVLink (900 GB/s per direction per GPU nominal).  NCCL on the same GPUs is
+  timed beside it as a comparison point (not the oracle, not the baseline).
+* ``--impl reference``: the reference's own CPU path — gloo over TCP loopback, which is
+  what ref:src/nbdistributed/worker.py:146-147 selects without CUDA — on the box's host
+  cores, same metric and config (R or N local processes), on a bounded sample.
+
+``value`` is the whole-job figure: the sum over ranks of bus bytes (S * 2(R-1)/R each) per
+second with inputs resident in HBM; ``busbw_per_rank`` = value / ranks is the nccl-tests
+number that the 900 GB/s NVLink roofline applies to.  ``e2e`` is the same metric through the
+public call with pinned HOST buffers, H2D and D2H copies inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "all_reduce bus GB/s"
+UNIT = "GB/s"
+MSG_BYTES = 256 << 20          # per-rank message of the headline step
+EMU_RANKS = 8                  # ranks emulated on one GPU at N = 1
+NVLINK_PEAK_GBS = 900.0        # per direction per GPU, nominal (BASELINE.json north_star)
+HBM_FALLBACK_GBS = 6650.0      # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def log(msg: str) -> None:
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(f"[bench {time.strftime('%H:%M:%S')}] {msg}", file=sys.stderr, flush=True)
+
+
+def bus_factor(ranks: int) -> float:
+    return 2.0 * (ranks - 1) / ranks
+
+
+def measured_hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(key: str):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(key)
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    REASONS = {
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+        0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+        0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, device_index: int = 0, period_s: float = 0.002):
+        self.device_index = device_index
+        self.period_s = period_s
+        self.samples = []
+        self.reason_mask = 0
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        self._nv = None
+
+    def start(self):
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            self._nv = nv
+            self._h = nv.nvmlDeviceGetHandleByIndex(self.device_index)
+            self.max_mhz = int(nv.nvmlDeviceGetMaxClockInfo(self._h, nv.NVML_CLOCK_SM))
+        except Exception:
+            self._nv = None
+            return self
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
+        return self
+
+    def _run(self):
+        nv = self._nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                try:
+                    self.reason_mask |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                except Exception:
+                    self.reason_mask |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+            except Exception:
+                pass
+            self._stop.wait(self.period_s)
+
+    def stop(self):
+        self._stop.set()
+        if self._thread:
+            self._thread.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        s = sorted(self.samples)
+        reasons = [name for bit, name in self.REASONS.items() if self.reason_mask & bit and name != "gpu_idle"]
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(s)}
+
+
+def physical_gpu_index(local_index: int) -> int:
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_index])
+        except Exception:
+            return local_index
+    return local_index
+
+
+# --------------------------------------------------------------------------------------
+# CPU baseline: the reference's gloo path on this box's host cores (bounded sample)
+# --------------------------------------------------------------------------------------
+def gloo_cpu_baseline(ranks: int, msg_bytes: int, iters: int, warmup: int):
+    """Seconds per all_reduce (max over ranks) of the reference's CPU path: `ranks` local
+    processes, backend gloo, fp32 tensors of msg_bytes each (oracle/gloo_runner.py)."""
+    from oracle.gloo_runner import time_gloo
+
+    numel = msg_bytes // 4
+    t = time_gloo(ranks, [{"kind": "all_reduce", "dtype": "f32", "numel": numel, "iters": iters, "warmup": warmup}],
+                  timeout=240.0)[0]
+    return t
+
+
+def cpu_baseline_object(ranks: int, msg_bytes: int):
+    sample_bytes = min(msg_bytes, 64 << 20)  # bounded: ~10-30 s of CPU work including start-up
+    iters, warm = 5, 1
+    try:
+        t = gloo_cpu_baseline(ranks, sample_bytes, iters, warm)
+    except Exception as e:  # noqa: BLE001 - the bench line must still be printed
+        return {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
+                "sample": f"gloo baseline failed: {str(e)[:160]}"}
+    per_rank = sample_bytes * bus_factor(ranks) / t / 1e9
+    return {
+        "value": round(per_rank * ranks, 3), "unit": UNIT, "busbw_per_rank": round(per_rank, 3),
+        "cores": os.cpu_count(), "processes": ranks, "kind": "reference",
+        "sample": f"gloo (torch {_torch_version()}) all_reduce fp32 SUM, {sample_bytes >> 20} MiB per rank, {ranks} local "
+                  f"processes over TCP loopback, {warm} warm-up + {iters} timed iterations, {t * 1e3:.1f} ms/iter; each gloo "
+                  f"rank runs 1 reduction thread + 1 I/O thread",
+    }
+
+
+def _torch_version():
+    import torch
+
+    return torch.__version__
+
+
+# --------------------------------------------------------------------------------------
+# our arm, N = 1: emulated ranks on one GPU (HBM-bound 1-GPU row)
+# --------------------------------------------------------------------------------------
+def run_ours_single(args):
+    import torch
+
+    from nbdistributed_b200 import capi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 backend has no CPU fallback "
+                         "(use --impl reference for the gloo CPU arm)")
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    R, S = EMU_RANKS, MSG_BYTES
+    numel = S // 4
+    grp = capi.EmuGroup(R, device=0)
+    g = torch.Generator(device=dev)
+    sends = []
+    for r in range(R):
+        g.manual_seed(1234 + r)
+        sends.append(torch.randn(numel, generator=g, device=dev, dtype=torch.float32))
+    recvs = [torch.empty_like(s) for s in sends]
+
+    def step():
+        grp.all_reduce(sends, recvs)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    grp.async_error()
+    algo = grp.last_algo()
+
+    sampler = ClockSampler(physical_gpu_index(0)).start()
+    l0 = capi.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    launches = capi.launch_count() - l0
+    clocks = sampler.stop()
+    grp.async_error()
+    ms = ev0.elapsed_time(ev1) / args.steps
+    per_rank = S * bus_factor(R) / (ms * 1e-3) / 1e9
+    value = per_rank * R
+
+    # correctness of what was timed: spot-check against the oracle (rank order, bit-exact)
+    import numpy as np
+
+    from oracle import collectives_oracle as O
+
+    idx = torch.from_numpy(np.random.default_rng(0).integers(0, numel, 8192)).to(dev)
+    sample = [s[idx].cpu().numpy() for s in sends]
+    want = O.reduce_rank_order(sample, "f32")
+    for r in (0, R - 1):
+        if not np.array_equal(recvs[r][idx].cpu().numpy().view(np.uint32), want.view(np.uint32)):
+            raise SystemExit("bench.py: timed all_reduce does not match the oracle")
+
+    # ---- end to end: pinned host buffers -> H2D -> all_reduce -> D2H, every step --------
+    host_in = [torch.empty(numel, dtype=torch.float32).pin_memory() for _ in range(R)]
+    host_out = [torch.empty(numel, dtype=torch.float32).pin_memory() for _ in range(R)]
+    for r in range(R):
+        host_in[r].copy_(sends[r])
+    e2e_steps = max(2, min(args.steps, 5))
+
+    def e2e_step():
+        for r in range(R):
+            sends[r].copy_(host_in[r], non_blocking=True)
+        grp.all_reduce(sends, recvs)
+        for r in range(R):
+            host_out[r].copy_(recvs[r], non_blocking=True)
+
+    e2e_step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ev0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    ev1.record()
+    torch.cuda.synchronize()
+    e2e_ms = max(ev0.elapsed_time(ev1), (time.perf_counter() - t0) * 1e3) / e2e_steps
+    e2e_value = S * bus_factor(R) * R / (e2e_ms * 1e-3) / 1e9
+
+    # ---- roofline of the dominant kernel (the all_reduce launch itself) ------------------
+    peak, peak_src = measured_hbm_peak()
+    alg_bytes = 2.0 * R * S  # every rank's input read once + every rank's output written once
+    achieved = alg_bytes / (ms * 1e-3) / 1e9
+    traffic = recorded_traffic(f"emu{R}_allreduce_f32_{S >> 20}MiB")
+
+    extras = {}
+    if not args.no_sweep:
+        extras["sweep"] = emu_sweep(torch, grp, dev, R)
+    del host_in, host_out
+    grp.close()
+
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "busbw_per_rank": round(per_rank, 2),
+        "config": {"workload": f"all_reduce fp32 SUM, {S >> 20} MiB per rank, {R} ranks emulated on 1 GPU "
+                               f"(one cooperative launch; peers = local buffers), out of place, algo={algo}",
+                   "ranks": R, "message_bytes": S, "l2": "inputs (2 GiB) larger than L2; no reuse between steps",
+                   "value_definition": "sum over ranks of S*2(R-1)/R bytes per second"},
+        "clocks": clocks,
+        "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": R * S, "d2h_bytes_per_step": R * S,
+                "ms_per_step": round(e2e_ms, 3), "api": "nbd_emu_all_reduce via nbdistributed_b200.capi.EmuGroup"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg_bytes,
+                     "kernel": "nbd::k_allreduce_twoshot<float,true,8>",
+                     "note": "algorithmic bytes = minimal 2*R*S; the staged algorithm itself moves (5R-2)*S"},
+    }
+    line.update(extras)
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_object(R, S)
+    return line
+
+
+def emu_sweep(torch, grp, dev, R):
+    """Message-size sweep on the emulated group (extra information, outside the timed region)."""
+    out = []
+    for kind in ("all_reduce", "broadcast"):
+        for dt, es in ((torch.float32, 4), (torch.bfloat16, 2)):
+            for nbytes in (4 << 10, 64 << 10, 1 << 20, 16 << 20, 64 << 20, 256 << 20):
+                n = nbytes // es
+                bufs = [torch.ones(n, device=dev, dtype=dt) for _ in range(R)]
+                outs = [torch.empty_like(b) for b in bufs]
+                iters = 50 if nbytes <= (1 << 20) else 10
+                fn = (lambda: grp.all_reduce(bufs, outs)) if kind == "all_reduce" else (lambda: grp.broadcast(bufs, root=0))
+                for _ in range(3):
+                    fn()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(iters):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize()
+                us = e0.elapsed_time(e1) * 1e3 / iters
+                factor = bus_factor(R) if kind == "all_reduce" else 1.0
+                out.append({"op": kind, "dtype": str(dt).replace("torch.", ""), "bytes": nbytes, "us": round(us, 2),
+                            "busbw_per_rank": round(nbytes * factor / us / 1e3, 2), "algo": grp.last_algo()})
+                del bufs, outs
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# our arm, N > 1: one process per GPU through torch.distributed backend "b200"
+# --------------------------------------------------------------------------------------
+def _time_collective(torch, dist, fn, iters, warmup, cpu_group):
+    """ms per call: CUDA events on the launching stream, barrier + synchronize on both sides,
+    max over ranks."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier(group=cpu_group)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier(group=cpu_group)
+    t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
+    return float(t.item())
+
+
+def run_ours_multi(args):
+    import torch
+    import torch.distributed as dist
+
+    from nbdistributed_b200 import backend as B
+    from nbdistributed_b200 import worker_init as W
+
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    ns = W.init_worker(rank, world, os.environ.get("MASTER_ADDR", "127.0.0.1"), os.environ.get("MASTER_PORT", "29500"),
+                       gpu_id=local, backend="b200")
+    os.environ["LOCAL_RANK"] = str(local)
+    dev = torch.device("cuda", local)
+    cpu_group = dist.new_group(backend="gloo")
+    S = MSG_BYTES
+    numel = S // 4
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    src = torch.randn(numel, generator=g, device=dev, dtype=torch.float32) * 0.01
+    x = src.clone()
+    be = B.get_backend()
+
+    def step():
+        dist.all_reduce(x)
+
+    W0 = max(args.warmup, 3)
+    for _ in range(W0):
+        step()
+    torch.cuda.synchronize()
+    algo = be.last_algo()
+    # correctness of the timed op: one fresh all_reduce against gloo on the same inputs
+    x.copy_(src)
+    dist.all_reduce(x)
+    ref = src.cpu()
+    dist.all_reduce(ref, group=cpu_group)
+    tol = 1e-6 * world * float(src.abs().max()) + 1e-12
+    if not torch.allclose(x.cpu(), ref, rtol=0, atol=tol * 8):
+        raise SystemExit("bench.py: b200 all_reduce differs from gloo beyond the fp32 tolerance")
+    x.copy_(src)
+
+    sampler = ClockSampler(physical_gpu_index(local)).start() if rank == 0 else None
+    l0 = B.launch_count()
+    torch.cuda.synchronize()
+    dist.barrier(group=cpu_group)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier(group=cpu_group)
+    launches = B.launch_count() - l0
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
+    ms = float(t.item())
+    per_rank = S * bus_factor(world) / (ms * 1e-3) / 1e9
+
+    # ---- end to end: pinned host -> H2D -> dist.all_reduce -> D2H, each step -------------
+    h_in = torch.empty(numel, dtype=torch.float32).pin_memory()
+    h_out = torch.empty(numel, dtype=torch.float32).pin_memory()
+    h_in.copy_(src)
+
+    def e2e_step():
+        x.copy_(h_in, non_blocking=True)
+        dist.all_reduce(x)
+        h_out.copy_(x, non_blocking=True)
+
+    log(f"timed region done: {ms:.3f} ms/step, busbw/rank {per_rank:.1f} GB/s; measuring e2e")
+    e2e_ms = _time_collective(torch, dist, e2e_step, max(2, min(args.steps, 5)), 1, cpu_group)
+    e2e_per_rank = S * bus_factor(world) / (e2e_ms * 1e-3) / 1e9
+
+    extras = {}
+    if not args.no_sweep:
+        log("message-size sweep")
+        extras["sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be)
+    if not args.no_nccl:
+        log("NCCL comparison point")
+        extras["nccl"] = nccl_comparison(torch, dist, dev, world, cpu_group, S)
+    log("collectives done; tearing down")
+
+    line = None
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(per_rank * world, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": W0, "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "busbw_per_rank": round(per_rank, 2),
+            "config": {"workload": f"all_reduce fp32 SUM, {S >> 20} MiB per rank, {world} ranks (one process per GPU) "
+                                   f"through dist.all_reduce on backend '{ns['__backend__']}', in place, algo={algo}",
+                       "ranks": world, "message_bytes": S, "l2": "message (256 MiB) larger than L2",
+                       "value_definition": "sum over ranks of S*2(N-1)/N bytes per second"},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_per_rank * world, 2), "unit": UNIT, "h2d_bytes_per_step": S * world,
+                    "d2h_bytes_per_step": S * world, "ms_per_step": round(e2e_ms, 3),
+                    "api": "torch.distributed.all_reduce (backend b200) on a tensor copied from pinned host memory"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "nvlink", "achieved": round(per_rank, 1), "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
+                         "frac": round(per_rank / NVLINK_PEAK_GBS, 4), "traffic": None,
+                         "peak_source": "nominal NVLink 5 per direction per GPU (BASELINE.json); measured peer copy on this "
+                                        "pool: 770 GB/s (B200_PROFILING.md)",
+                         "algorithmic_bytes_per_launch": S * bus_factor(world),
+                         "kernel": "nbd::k_allreduce_oneshot/twoshot<float,true,1>"},
+        }
+        line.update(extras)
+    dist.barrier(group=cpu_group)
+    W.shutdown_worker()
+    if rank == 0 and not args.no_cpu_baseline:
+        log("gloo CPU baseline")
+        line["cpu_baseline"] = cpu_baseline_object(world, S)
+    return line
+
+
+def multi_sweep(torch, dist, dev, world, cpu_group, be):
+    out = []
+    for kind in ("all_reduce", "broadcast"):
+        for dt, es in ((torch.float32, 4), (torch.bfloat16, 2)):
+            for nbytes in (4 << 10, 64 << 10, 1 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30):
+                if dt == torch.bfloat16 and nbytes not in (4 << 10, 1 << 20, 64 << 20, 1 << 30):
+                    continue
+                buf = torch.ones(nbytes // es, device=dev, dtype=dt)
+                iters = 100 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 5)
+                fn = (lambda: dist.all_reduce(buf)) if kind == "all_reduce" else (lambda: dist.broadcast(buf, src=0))
+                ms = _time_collective(torch, dist, fn, iters, 5 if nbytes <= (1 << 20) else 2, cpu_group)
+                factor = bus_factor(world) if kind == "all_reduce" else 1.0
+                out.append({"op": kind, "dtype": str(dt).replace("torch.", ""), "bytes": nbytes, "us": round(ms * 1e3, 2),
+                            "busbw_per_rank": round(nbytes * factor / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
+                del buf
+    return out
+
+
+def nccl_comparison(torch, dist, dev, world, cpu_group, S):
+    """NCCL (torch-bundled) on the same GPUs, same sizes: comparison point only."""
+    try:
+        pg = dist.new_group(backend="nccl")
+        out = []
+        for nbytes in (4 << 10, 1 << 20, 64 << 20, S, 1 << 30):
+            buf = torch.ones(nbytes // 4, device=dev, dtype=torch.float32)
+            iters = 100 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 5)
+            ms = _time_collective(torch, dist, lambda: dist.all_reduce(buf, group=pg), iters, 5, cpu_group)
+            out.append({"op": "all_reduce", "dtype": "float32", "bytes": nbytes, "us": round(ms * 1e3, 2),
+                        "busbw_per_rank": round(nbytes * bus_factor(world) / (ms * 1e-3) / 1e9, 2)})
+            del buf
+        return {"version": ".".join(map(str, torch.cuda.nccl.version())), "results": out}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": str(e)[:200]}
+
+
+# --------------------------------------------------------------------------------------
+# reference arm: the reference's CPU path (gloo) on the host cores
+# --------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None  # under torchrun only rank 0 works; the others exit 0
+    n = max(1, args.gpus)
+    ranks = EMU_RANKS if n == 1 else n
+    sample_bytes = min(MSG_BYTES, 64 << 20)
+    warm, iters = max(1, min(args.warmup, 3)), max(1, min(args.steps, 10))
+    t = gloo_cpu_baseline(ranks, sample_bytes, iters, warm)
+    per_rank = sample_bytes * bus_factor(ranks) / t / 1e9
+    value = round(per_rank * ranks, 3)
+    sample = (f"gloo all_reduce fp32 SUM, {sample_bytes >> 20} MiB per rank (bounded sample of the {MSG_BYTES >> 20} MiB "
+              f"step), {ranks} local processes over TCP loopback, {warm} warm-up + {iters} timed iterations")
+    return {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n, "steps": iters, "warmup": warm,
+        "ms_per_step": round(t * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "busbw_per_rank": round(per_rank, 3),
+        "config": {"workload": f"all_reduce fp32 SUM, {ranks} ranks, reference CPU path (backend gloo, "
+                               f"ref:src/nbdistributed/worker.py:146-147)", "ranks": ranks, "message_bytes": sample_bytes,
+                   "value_definition": "sum over ranks of S*2(R-1)/R bytes per second"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": os.cpu_count(), "processes": ranks, "kind": "reference",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the message-size sweep (extra keys)")
+    ap.add_argument("--no-nccl", action="store_true", help="skip the NCCL comparison point (N > 1)")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip timing gloo on the host cores")
+    args = ap.parse_args()
+    args.steps = max(1, args.steps)
+
+    # stdout carries exactly ONE JSON line: libraries that print to fd 1 (NCCL's version
+    # banner, for one) are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    if args.impl == "reference":
+        line = run_reference(args)
+    elif int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        line = run_ours_multi(args)
+    else:
+        if args.gpus > 1:
+            raise SystemExit("bench.py --gpus N>1 must be launched with python -m torch.distributed.run "
+                             "--nproc-per-node N (one process per GPU)")
+        line = run_ours_single(args)
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
+    os.close(real_stdout)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -117,6 +117,11 @@ def _time_job(job: Dict[str, Any], rank: int, world: int) -> float:
 
 
 def _worker(rank: int, world: int, port: int, jobs: List[Dict[str, Any]], mode: str, q) -> None:
+    # a parent launched by torchrun exports TORCHELASTIC_* (agent store, restart counts, ...);
+    # this group is its own rendezvous, exactly like a worker.py process
+    for k in [k for k in os.environ if k.startswith("TORCHELASTIC_") or k in ("GROUP_RANK", "ROLE_RANK", "LOCAL_WORLD_SIZE",
+                                                                              "ROLE_WORLD_SIZE", "GROUP_WORLD_SIZE")]:
+        os.environ.pop(k, None)
     os.environ["RANK"] = str(rank)
     os.environ["LOCAL_RANK"] = str(rank)
     os.environ["WORLD_SIZE"] = str(world)

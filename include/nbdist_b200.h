@@ -185,6 +185,26 @@ int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends,
                            int op, void* stream);
 int nbd_emu_barrier(nbd_comm_t any, void* stream);
 
+/* ---- allocation-free variant ------------------------------------------------
+ * No counterpart in the reference.
+ * The all-reduce of nbd_emu_all_reduce (world_size buffers that all live on the CURRENT
+ * device, reduced in ascending rank order, every recvs[r] receiving the result) for callers
+ * that cannot allocate device memory at the time of the call — e.g. a process whose HBM
+ * is already owned by another allocator, or a latency-critical loop that cannot take the
+ * device-wide stall of cudaMalloc/cudaFree.  It needs no communicator: flags, staging and
+ * clocks live in a fixed array inside the library (about 8.5 MiB of device memory on every
+ * GPU that loads the library, held until the process exits) and the call performs no
+ * cudaMalloc/cudaFree or any other allocating routine.
+ *  - at most NBD_NOALLOC_MAX_BYTES per rank; larger messages are rejected with
+ *    NBD_ERR_INVALID_ARGUMENT (use nbd_emu_all_reduce);
+ *  - the first call on a device looks up the array's device address; make that first call
+ *    before starting any stream capture on that device;
+ *  - all calls share the one array: order them on the GPU (same stream, or events).  Calls
+ *    whose device work overlaps race on it and produce wrong results. */
+#define NBD_NOALLOC_MAX_BYTES (1u << 20)
+int nbd_local_all_reduce_noalloc(const void* const* sends, void* const* recvs, int world_size,
+                                 size_t count, int dtype, int op, void* stream);
+
 /* ---- introspection for benches/tests ------------------------------------- */
 
 /* Number of kernels this library has launched in this process so far. */

@@ -34,8 +34,10 @@ SYMBOLS = [
     "nbd_emu_create", "nbd_emu_destroy",
     "nbd_all_reduce", "nbd_broadcast", "nbd_all_gather", "nbd_reduce_scatter", "nbd_barrier",
     "nbd_emu_all_reduce", "nbd_emu_broadcast", "nbd_emu_all_gather", "nbd_emu_reduce_scatter", "nbd_emu_barrier",
+    "nbd_local_all_reduce_noalloc",
     "nbd_launch_count", "nbd_last_algo",
 ]
+NOALLOC_MAX_BYTES = 1 << 20
 
 
 class NbdError(RuntimeError):
@@ -87,6 +89,7 @@ def load() -> C.CDLL:
         "nbd_emu_all_gather": (i, [vp, pp, pp, sz, i, vp]),
         "nbd_emu_reduce_scatter": (i, [vp, pp, pp, sz, i, i, vp]),
         "nbd_emu_barrier": (i, [vp, vp]),
+        "nbd_local_all_reduce_noalloc": (i, [pp, pp, i, sz, i, i, vp]),
         "nbd_launch_count": (u64, []),
         "nbd_last_algo": (C.c_char_p, [vp]),
     }
@@ -131,6 +134,17 @@ def _stream_handle(stream) -> int:
 
     s = stream if stream is not None else torch.cuda.current_stream()
     return int(s.cuda_stream)
+
+
+def local_all_reduce_noalloc(sends, recvs=None, op: int = SUM, stream=None) -> None:
+    """nbd_local_all_reduce_noalloc on torch CUDA tensors of the current device (index = rank).
+    Uses the library's fixed scratch array: no communicator, no allocation; at most
+    NOALLOC_MAX_BYTES per rank; calls must not overlap on the GPU."""
+    lib = load()
+    recvs = sends if recvs is None else recvs
+    t = sends[0]
+    check(lib.nbd_local_all_reduce_noalloc(_ptr_array(sends), _ptr_array(recvs), len(sends), t.numel(),
+                                           torch_dtype_code(t.dtype), op, _stream_handle(stream)))
 
 
 class EmuGroup:

@@ -13,6 +13,7 @@
 #include <unistd.h>
 
 #include <atomic>
+#include <mutex>
 #include <string>
 
 #include "../../include/nbdist_b200.h"
@@ -864,3 +865,128 @@ int nbd_emu_barrier(nbd_comm_t any, void* stream) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// nbd_local_all_reduce_noalloc — all-reduce of R buffers on ONE GPU without any allocation
+// ---------------------------------------------------------------------------
+// For hosts that must not allocate when they call us: a process whose device memory is
+// already parcelled out to another allocator (a serving stack, torch's caching allocator
+// holding nearly all of HBM) where a driver allocation may fail or evict that allocator's
+// cache, and latency-sensitive loops for which the device-wide stall of cudaMalloc/cudaFree
+// is not acceptable.  The emulated-rank all-reduce normally takes its flags, staging and
+// clocks from arenas that nbd_emu_create() cudaMallocs; here they live in the file-scope
+// array below, which every GPU that loads this library carries until the process exits.
+//
+// Layout of g_noalloc_scratch (offsets in bytes):
+//   [0, R*kFlagBytes)                     flag arrays, one per rank
+//   [.., + R*256)                         LocalState per rank
+//   [.., + R*256)                         mailbox per rank (device-resident stand-in)
+//   [kNaStageOff, + R*kNaStageBytes)      staging, one per rank (two halves each)
+// The control part (everything before kNaStageOff) is zeroed on the caller's stream at the
+// start of every call: flags and clocks must start equal on all ranks, and a previous call
+// with another world size leaves them unequal.  Staging needs no clearing (always written
+// before it is read).  All calls share the one array, so two calls whose GPU work overlaps
+// (different streams, no ordering between them) corrupt each other.
+namespace {
+
+constexpr size_t kNaStageBytes = 1u << 20;  // per rank; half of it per pipeline step
+constexpr size_t kNaCtlBytes = (size_t)kMaxRanks * (kFlagBytes + 256 + 256);
+constexpr size_t kNaStageOff = (kNaCtlBytes + 255) / 256 * 256;
+constexpr size_t kNaTotalBytes = kNaStageOff + (size_t)kMaxRanks * kNaStageBytes;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaTotalBytes];
+
+constexpr int kNaMaxDevices = 64;
+struct NoAllocDevice {
+  bool ready = false;
+  unsigned char* base = nullptr;  // DEVICE address of g_noalloc_scratch on this device
+  nbd_comm plan;                  // host-only planning record (tunables, SM count); owns nothing
+};
+static NoAllocDevice g_na_dev[kNaMaxDevices];
+static std::mutex g_na_mu;
+
+// Once per device, with that device current.  g_noalloc_scratch named in host code is only a
+// host-side handle of the symbol; the address kernels can use comes from the runtime.
+static int noalloc_setup(int device, NoAllocDevice** out) {
+  std::lock_guard<std::mutex> lk(g_na_mu);
+  NoAllocDevice& d = g_na_dev[device];
+  if (!d.ready) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      cudaGetLastError();
+      return fail(NBD_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d: %s", device,
+                  cudaGetErrorString(e));
+    }
+    int sms = 0, coop = 0;
+    NBD_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    NBD_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device));
+    if (!coop) return fail(NBD_ERR_UNSUPPORTED, "device %d lacks cooperative launch", device);
+    d.base = static_cast<unsigned char*>(ptr);
+    d.plan.device = device;
+    d.plan.num_sms = sms;
+    d.plan.emu = true;
+    d.plan.connected = true;
+    d.ready = true;
+  }
+  *out = &d;
+  return NBD_OK;
+}
+
+}  // namespace
+
+extern "C" int nbd_local_all_reduce_noalloc(const void* const* sends, void* const* recvs, int world_size, size_t count,
+                                            int dtype, int op, void* stream) {
+  int rc = check_reduce_args(dtype, op);
+  if (rc != NBD_OK) return rc;
+  if (world_size < 1 || world_size > kMaxRanks)
+    return fail(NBD_ERR_INVALID_ARGUMENT, "world_size %d not in [1,%d]", world_size, kMaxRanks);
+  const u64 bytes = (u64)count * nbd_dtype_size(dtype);
+  if (bytes > (u64)NBD_NOALLOC_MAX_BYTES)
+    return fail(NBD_ERR_INVALID_ARGUMENT,
+                "nbd_local_all_reduce_noalloc: %llu bytes per rank exceeds the fixed scratch limit of %llu bytes "
+                "(NBD_NOALLOC_MAX_BYTES); use nbd_emu_all_reduce for larger messages",
+                (unsigned long long)bytes, (unsigned long long)NBD_NOALLOC_MAX_BYTES);
+  if (count == 0) return NBD_OK;
+  if (!sends || !recvs) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL pointer array");
+  for (int r = 0; r < world_size; ++r)
+    if (!sends[r] || !recvs[r]) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer for rank %d", r);
+  int device = 0;
+  NBD_CUDA(cudaGetDevice(&device));
+  if (device < 0 || device >= kNaMaxDevices) return fail(NBD_ERR_INVALID_ARGUMENT, "device %d out of range", device);
+  NoAllocDevice* d = nullptr;
+  if ((rc = noalloc_setup(device, &d)) != NBD_OK) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (world_size == 1) {
+    if (sends[0] != recvs[0]) NBD_CUDA(cudaMemcpyAsync(recvs[0], sends[0], bytes, cudaMemcpyDeviceToDevice, s));
+    return NBD_OK;
+  }
+
+  std::lock_guard<std::mutex> lk(g_na_mu);  // d->plan is shared host state
+  unsigned char* base = d->base;
+  Pack<kMaxRanks> pk;
+  memset(&pk, 0, sizeof(pk));
+  unsigned char* states = base + (size_t)kMaxRanks * kFlagBytes;
+  unsigned char* mboxes = states + (size_t)kMaxRanks * 256;
+  for (int r = 0; r < world_size; ++r) {
+    RankCtx& x = pk.ctx[r];
+    x.rank = r;
+    x.world = world_size;
+    for (int p = 0; p < world_size; ++p) {
+      x.flags[p] = reinterpret_cast<u64*>(base + (size_t)p * kFlagBytes);
+      x.stage[p] = reinterpret_cast<char*>(base + kNaStageOff + (size_t)p * kNaStageBytes);
+    }
+    x.state = reinterpret_cast<LocalState*>(states + (size_t)r * 256);
+    x.mbox = reinterpret_cast<HostMailbox*>(mboxes + (size_t)r * 256);
+    x.half_bytes = (kNaStageBytes / 2) / kUnit * kUnit;
+    x.timeout_ns = 10ull * 1000000000ull;
+    pk.buf[r].send = static_cast<const char*>(sends[r]);
+    pk.buf[r].recv = static_cast<char*>(recvs[r]);
+  }
+  d->plan.world = world_size;
+  d->plan.ctx.half_bytes = pk.ctx[0].half_bytes;
+  Plan p = plan_all_reduce(&d->plan, bytes, op, world_size);
+  // flags, clocks and mailboxes start from zero on every call (see the layout note above)
+  NBD_CUDA(cudaMemsetAsync(base, 0, kNaCtlBytes, s));
+  return launch_reduce<kMaxRanks>(p.op.algo == 1 ? K_AR1 : K_AR2, dtype, op, p.nblocks, world_size, s, pk, &p.op);
+}

@@ -46,7 +46,8 @@ typedef enum {
   NBD_ERR_TIMEOUT = -4,   /* a peer never arrived at a flag barrier */
   NBD_ERR_ABORTED = -5,
   NBD_ERR_UNSUPPORTED = -6, /* dtype/op combination not implemented */
-  NBD_ERR_INTERNAL = -7
+  NBD_ERR_INTERNAL = -7,
+  NBD_ERR_MISMATCH = -8 /* ranks disagreed on the buffers of a zero-copy collective */
 } nbd_result;
 
 /* Element types.  Copy collectives (broadcast, all_gather) are byte moves and
@@ -119,9 +120,25 @@ int nbd_comm_world_size(nbd_comm_t comm);
 int nbd_comm_set_timeout_ms(nbd_comm_t comm, uint64_t timeout_ms);
 /* Tuning knobs: "blocks" (max CTAs per collective), "ar1_max_bytes"
  * (one-shot/two-shot all-reduce switch), "bcast_direct_max_bytes",
- * "chunk_bytes" (pipeline chunk).  value 0 restores the default. */
+ * "chunk_bytes" (pipeline chunk), "zero_copy_off" (1 = always stage),
+ * "zc_min_bytes" (smallest message that goes zero-copy).  value 0 restores
+ * the default. */
 int nbd_comm_set_tunable(nbd_comm_t comm, const char* name, uint64_t value);
 int nbd_comm_get_tunable(nbd_comm_t comm, const char* name, uint64_t* value);
+
+/* ---- symmetric memory (zero-copy collectives) --------------------------------
+ * Replaces nothing in the reference; it is the backend side of c10d's
+ * Backend::allocateTensor / supportsTensorAlloc ($TORCH/.../Backend.hpp:492-503), which FSDP
+ * uses for its all_gather / reduce_scatter buffers.  A buffer obtained here is mapped by every
+ * peer, so collectives on it skip the staging arena: barrier, one streaming pass over peer
+ * memory, barrier.  Allocation is collective: every rank calls nbd_mem_alloc in the same
+ * order with the same size, all-gathers the handles over its rendezvous, then calls
+ * nbd_mem_connect.  Ranks must pass the same offset within the same allocation to a
+ * collective (checked on the device; a mismatch surfaces as NBD_ERR_MISMATCH).  Collectives on
+ * ordinary (unregistered) pointers keep using the staged kernels. */
+int nbd_mem_alloc(nbd_comm_t comm, size_t bytes, void** ptr, void* handle_out /*NBD_HANDLE_BYTES*/);
+int nbd_mem_connect(nbd_comm_t comm, void* ptr, const void* all_handles);
+int nbd_mem_free(nbd_comm_t comm, void* ptr);
 
 /* ---- emulated ranks: R ranks on ONE device, one process -------------------
  * The same device code as above, with every "peer" arena living on the same

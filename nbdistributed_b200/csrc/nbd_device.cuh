@@ -69,6 +69,25 @@ struct Pack {
   RankBufs buf[NCTX];
 };
 
+// Zero-copy collectives: every rank's user buffers are directly addressable (registered
+// symmetric memory between processes, or simply local for emulated ranks).  send[p] / recv[p]
+// are rank p's buffers of THIS operation in our address space (null where not needed).
+struct ZcPtrs {
+  const char* send[kMaxRanks];
+  char* recv[kMaxRanks];
+  u64 desc[6];  // {send registration, send offset, recv registration, recv offset, bytes, op tag}
+};
+
+template <int NCTX>
+struct PackZc {
+  RankCtx ctx[NCTX];
+  ZcPtrs z;
+};
+
+// Operation descriptors for the symmetric-use check live in flag rows no grid ever reaches
+// (grids are capped well below kDescRow CTAs): row kDescRow + src holds rank src's 8 words.
+constexpr int kDescRow = kMaxBlocks - 2 * kMaxRanks;
+
 struct OpParams {
   u64 bytes;        // all_reduce/broadcast: message bytes; all_gather /
                     // reduce_scatter: bytes of ONE rank's shard

@@ -409,6 +409,171 @@ k_broadcast(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   kernel_end(c, op.nchunks, op.nchunks);
 }
 
+
+// ---------------------------------------------------------------------------
+// Zero-copy kernels: user buffers of every rank are peer-addressable, so there is no
+// staging and no chunk pipeline — barrier, one streaming pass, barrier.  Bytes moved are the
+// algorithmic minimum; both NVLink directions are busy for the whole pass.
+// ---------------------------------------------------------------------------
+
+// Ranks must pass the same registered region/offset/size: CTA 0 publishes this rank's
+// descriptor to every peer before the opening barrier and compares afterwards.
+template <int NCTX>
+__device__ __forceinline__ void zc_publish_desc(const RankCtx& c, const ZcPtrs& z, u64 tag) {
+  if (NCTX != 1 || blockIdx.x != 0) return;
+  const int t = threadIdx.x;
+  if (t < c.world && t != c.rank) {
+    volatile u64* d = c.flags[t] + (u64)(kDescRow + c.rank) * kMaxRanks;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) d[j] = z.desc[j];
+    d[6] = tag;
+  }
+}
+
+template <int NCTX>
+__device__ __forceinline__ void zc_check_desc(const RankCtx& c, const ZcPtrs& z, u64 tag) {
+  if (NCTX != 1 || blockIdx.x != 0) return;
+  const int t = threadIdx.x;
+  if (t < c.world && t != c.rank) {
+    const volatile u64* d = c.flags[c.rank] + (u64)(kDescRow + t) * kMaxRanks;
+    bool same = (d[6] == tag);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) same = same && (d[j] == z.desc[j]);
+    if (!same) {
+      volatile HostMailbox* mb = c.mbox;
+      mb->error = 8;  // -NBD_ERR_MISMATCH
+    }
+  }
+}
+
+// all_reduce: rank r reduces shard r straight out of every rank's send buffer and writes the
+// result straight into every rank's recv buffer.  Wire per GPU: (N-1)/N*S in, (N-1)/N*S out,
+// concurrently.  In place is safe: only rank r reads or writes shard r of any buffer.
+template <typename T, bool SUM, int NCTX>
+__global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
+k_allreduce_zc(const __grid_constant__ PackZc<NCTX> pk, const OpParams op) {
+  const int ci = ctx_index<NCTX>();
+  const RankCtx& c = pk.ctx[ci];
+  const ZcPtrs& z = pk.z;
+  const int N = c.world, r = c.rank;
+  KernelClock clk = kernel_begin(c);
+  zc_publish_desc<NCTX>(c, z, clk.epoch + 1);
+  flag_barrier(c, ++clk.epoch);
+  zc_check_desc<NCTX>(c, z, clk.epoch);
+
+  const u64 units = units_of(op.bytes);
+  const u64 su = (units + N - 1) / N;
+  const u64 first = (u64)r * su;
+  const u64 mine = first >= units ? 0 : (units - first < su ? units - first : su);
+  u64 lo, hi;
+  block_span(su, mine, lo, hi);
+  bool al = true;
+#pragma unroll
+  for (int k = 0; k < kMaxRanks; ++k)
+    if (k < N) al = al && ((reinterpret_cast<uintptr_t>(z.send[k]) | reinterpret_cast<uintptr_t>(z.recv[k])) & (kUnit - 1)) == 0;
+  for (u64 i = first + lo + threadIdx.x; i < first + hi; i += kThreads) {
+    uint4 v[kMaxRanks];
+#pragma unroll
+    for (int k = 0; k < kMaxRanks; ++k)
+      if (k < N) v[k] = region_ld(make_region(z.send[k], op.bytes), al, i);
+    Reducer<T> R;
+    R.init(v[0]);
+#pragma unroll
+    for (int k = 1; k < kMaxRanks; ++k)
+      if (k < N) R.template add<SUM>(v[k], op.op);
+    const uint4 out = R.result(op.avg, N);
+#pragma unroll
+    for (int k = 0; k < kMaxRanks; ++k) {
+      if (k < N) {
+        int p = r + k;  // own buffer first, then peers in rotated order
+        if (p >= N) p -= N;
+        region_st(make_region(z.recv[p], op.bytes), al, i, out);
+      }
+    }
+  }
+  flag_barrier(c, ++clk.epoch);
+  kernel_end(c, 2, 0);
+}
+
+// reduce_scatter: rank r reduces its shard out of every rank's send buffer into its own
+// (local, possibly unregistered) recv.  op.bytes = shard bytes.
+template <typename T, bool SUM, int NCTX>
+__global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
+k_reduce_scatter_zc(const __grid_constant__ PackZc<NCTX> pk, const OpParams op) {
+  const int ci = ctx_index<NCTX>();
+  const RankCtx& c = pk.ctx[ci];
+  const ZcPtrs& z = pk.z;
+  const int N = c.world, r = c.rank;
+  KernelClock clk = kernel_begin(c);
+  zc_publish_desc<NCTX>(c, z, clk.epoch + 1);
+  flag_barrier(c, ++clk.epoch);
+  zc_check_desc<NCTX>(c, z, clk.epoch);
+
+  const u64 units = units_of(op.bytes);
+  u64 lo, hi;
+  block_span(units, units, lo, hi);
+  const Region dst = make_region(z.recv[r], op.bytes);
+  const bool ald = region_aligned(dst);
+  for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
+    uint4 v[kMaxRanks];
+#pragma unroll
+    for (int k = 0; k < kMaxRanks; ++k) {
+      if (k < N) {
+        const Region src = make_region(z.send[k] + (u64)r * op.bytes, op.bytes);
+        v[k] = region_ld(src, region_aligned(src), i);
+      }
+    }
+    Reducer<T> R;
+    R.init(v[0]);
+#pragma unroll
+    for (int k = 1; k < kMaxRanks; ++k)
+      if (k < N) R.template add<SUM>(v[k], op.op);
+    region_st(dst, ald, i, R.result(op.avg, N));
+  }
+  flag_barrier(c, ++clk.epoch);  // nobody may overwrite its send buffer before all have read it
+  kernel_end(c, 2, 0);
+}
+
+// all_gather.  algo 0 ("pull", send buffers registered): read every peer's shard straight
+// from its send buffer.  algo 1 ("push", recv buffers registered): write own shard straight
+// into every peer's recv buffer.  op.bytes = shard bytes.
+template <int NCTX>
+__global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
+k_all_gather_zc(const __grid_constant__ PackZc<NCTX> pk, const OpParams op) {
+  const int ci = ctx_index<NCTX>();
+  const RankCtx& c = pk.ctx[ci];
+  const ZcPtrs& z = pk.z;
+  const int N = c.world, r = c.rank;
+  KernelClock clk = kernel_begin(c);
+  zc_publish_desc<NCTX>(c, z, clk.epoch + 1);
+  flag_barrier(c, ++clk.epoch);
+  zc_check_desc<NCTX>(c, z, clk.epoch);
+
+  const u64 units = units_of(op.bytes);
+  u64 lo, hi;
+  block_span(units, units, lo, hi);
+  const Region own_src = make_region(z.send[r], op.bytes);
+#pragma unroll 1
+  for (u64 base = lo; base < hi; base += 4ull * kThreads) {
+    const u64 bhi = (base + 4ull * kThreads < hi) ? base + 4ull * kThreads : hi;
+#pragma unroll 1
+    for (int k = 0; k < N; ++k) {
+      int p = r + k;
+      if (p >= N) p -= N;
+      if (op.algo == 0) {
+        if (p == r && z.send[r] == z.recv[r] + (u64)r * op.bytes) continue;  // in place
+        copy_region_to_region<4>(make_region(z.recv[r] + (u64)p * op.bytes, op.bytes),
+                                 make_region(z.send[p], op.bytes), base, bhi);
+      } else {
+        if (p == r && z.send[r] == z.recv[r] + (u64)r * op.bytes) continue;
+        copy_region_to_region<4>(make_region(z.recv[p] + (u64)r * op.bytes, op.bytes), own_src, base, bhi);
+      }
+    }
+  }
+  flag_barrier(c, ++clk.epoch);
+  kernel_end(c, 2, 0);
+}
+
 // barrier: one CTA per rank, one flag round trip.
 template <int NCTX>
 __global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)

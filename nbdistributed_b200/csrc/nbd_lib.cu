@@ -15,6 +15,7 @@
 #include <atomic>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/nbdist_b200.h"
 #include "nbd_kernels.cuh"
@@ -73,6 +74,14 @@ struct nbd_comm {
   RankCtx ctx = {};
   // tunables (0 = default)
   uint64_t t_blocks = 0, t_ar1_max = 0, t_bcast_direct_max = 0, t_chunk = 0;
+  uint64_t t_zc_off = 0, t_zc_min = 0;  // zero-copy switch / size threshold
+  struct Registration {                 // symmetric memory: same index on every rank
+    char* base = nullptr;
+    size_t bytes = 0;
+    void* peer[kMaxRanks] = {};
+    bool connected = false;
+  };
+  std::vector<Registration> regs;
   uint64_t timeout_ms = 600000;
   const char* last_algo = "none";
 };
@@ -167,6 +176,13 @@ static void free_rank(nbd_comm* c) {
     for (int p = 0; p < c->world; ++p)
       if (p != c->rank && c->peer_base[p]) cudaIpcCloseMemHandle(c->peer_base[p]);
   }
+  for (auto& g : c->regs) {
+    if (!c->emu)
+      for (int p = 0; p < c->world; ++p)
+        if (p != c->rank && g.peer[p]) cudaIpcCloseMemHandle(g.peer[p]);
+    if (g.base) cudaFree(g.base);
+  }
+  c->regs.clear();
   if (c->arena) cudaFree(c->arena);
   if (c->state) cudaFree(c->state);
   if (c->mbox) cudaFreeHost(c->mbox);
@@ -186,6 +202,7 @@ const char* nbd_error_string(int r) {
     case NBD_ERR_ABORTED: return "communicator aborted";
     case NBD_ERR_UNSUPPORTED: return "unsupported dtype/op combination";
     case NBD_ERR_INTERNAL: return "internal error";
+    case NBD_ERR_MISMATCH: return "ranks passed different registered buffers/offsets/sizes to a zero-copy collective";
     default: return "unknown error";
   }
 }
@@ -335,6 +352,8 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "ar1_max_bytes")) return &c->t_ar1_max;
   if (!strcmp(name, "bcast_direct_max_bytes")) return &c->t_bcast_direct_max;
   if (!strcmp(name, "chunk_bytes")) return &c->t_chunk;
+  if (!strcmp(name, "zero_copy_off")) return &c->t_zc_off;
+  if (!strcmp(name, "zc_min_bytes")) return &c->t_zc_min;
   return nullptr;
 }
 
@@ -433,7 +452,7 @@ static int pick_blocks(const nbd_comm* c, u64 units_per_block_span, int emu_worl
   u64 cap = (u64)c->num_sms * kMinBlocksPerSM;
   if (emu_world > 1) cap /= (u64)emu_world;
   if (c->t_blocks && c->t_blocks < cap) cap = c->t_blocks;
-  if (cap > (u64)kMaxBlocks) cap = kMaxBlocks;
+  if (cap > (u64)kDescRow) cap = kDescRow;
   if (cap < 1) cap = 1;
   u64 want = ceil_div(units_per_block_span, (u64)kThreads * 4);
   if (want < 1) want = 1;
@@ -651,6 +670,87 @@ static int fill_pack_emu(Pack<kMaxRanks>& pk, EmuGroup* g, const void* const* se
   return NBD_OK;
 }
 
+
+// ---------------------------------------------------------------------------
+// zero-copy: registration lookup, planning, launch
+// ---------------------------------------------------------------------------
+static const u64 kDefZcMin = 256ull << 10;
+
+static bool zc_wanted(const nbd_comm* c, u64 bytes) {
+  return !c->t_zc_off && bytes >= (c->t_zc_min ? c->t_zc_min : kDefZcMin);
+}
+
+// index of the connected registration that contains [ptr, ptr+bytes), or -1
+static int find_reg(const nbd_comm* c, const void* ptr, u64 bytes, u64* off) {
+  const char* p = static_cast<const char*>(ptr);
+  for (size_t k = 0; k < c->regs.size(); ++k) {
+    const auto& g = c->regs[k];
+    if (g.connected && g.base && p >= g.base && p + bytes <= g.base + g.bytes) {
+      *off = (u64)(p - g.base);
+      return (int)k;
+    }
+  }
+  return -1;
+}
+
+enum ZKind { Z_AR, Z_RS };
+
+template <typename T, bool SUM, int NCTX>
+static const void* zc_reduce_kernel(ZKind k) {
+  return k == Z_AR ? (const void*)k_allreduce_zc<T, SUM, NCTX> : (const void*)k_reduce_scatter_zc<T, SUM, NCTX>;
+}
+
+static int launch_ptr(const void* kernel, int nblocks, int world, bool coop, cudaStream_t s, void* pk, OpParams* op) {
+  void* args[2] = {pk, (void*)op};
+  if (!coop) {
+    NBD_CUDA(cudaLaunchKernel(kernel, dim3(nblocks, 1, 1), dim3(kThreads, 1, 1), args, 0, s));
+  } else {
+    NBD_CUDA(cudaLaunchCooperativeKernel(kernel, dim3(nblocks, world, 1), dim3(kThreads, 1, 1), args, 0, s));
+  }
+  g_launches.fetch_add(1);
+  return NBD_OK;
+}
+
+template <int NCTX>
+static int launch_zc_reduce(ZKind k, int dtype, int op, int nblocks, int world, cudaStream_t s, PackZc<NCTX>& pk,
+                            OpParams* prm) {
+  int rc = NBD_OK;
+  const bool sum = (op == NBD_SUM || op == NBD_AVG);
+  const void* fn = nullptr;
+  NBD_SWITCH_DTYPE(dtype, fn = sum ? zc_reduce_kernel<T, true, NCTX>(k) : zc_reduce_kernel<T, false, NCTX>(k));
+  if (rc != NBD_OK) return rc;
+  return launch_ptr(fn, nblocks, world, NCTX != 1, s, &pk, prm);
+}
+
+static OpParams zc_params(const nbd_comm* c, u64 bytes, int op, int algo) {
+  OpParams p;
+  memset(&p, 0, sizeof(p));
+  p.bytes = bytes;
+  p.op = op;
+  p.avg = (op == NBD_AVG);
+  p.world = c->world;
+  p.algo = algo;
+  return p;
+}
+
+static int fill_zc_emu(PackZc<kMaxRanks>& pk, EmuGroup* g, const void* const* sends, void* const* recvs) {
+  memset(&pk, 0, sizeof(pk));
+  for (int r = 0; r < g->world; ++r) {
+    int rc = check_usable(g->comms[r]);
+    if (rc != NBD_OK) return rc;
+    pk.ctx[r] = g->comms[r]->ctx;
+    pk.z.send[r] = (const char*)sends[r];
+    pk.z.recv[r] = (char*)recvs[r];
+  }
+  return NBD_OK;
+}
+
+static void set_algo(nbd_comm* c, const char* name) {
+  c->last_algo = name;
+  if (c->emu)
+    for (int r = 0; r < c->group->world; ++r) c->group->comms[r]->last_algo = name;
+}
+
 extern "C" {
 
 // ---- real ranks -----------------------------------------------------------
@@ -669,6 +769,26 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
     c->last_algo = "local";
     if (send != recv) NBD_CUDA(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
     return NBD_OK;
+  }
+  {
+    u64 offs = 0, offr = 0;
+    const int ks = zc_wanted(c, bytes) ? find_reg(c, send, bytes, &offs) : -1;
+    const int kr = ks >= 0 ? find_reg(c, recv, bytes, &offr) : -1;
+    if (ks >= 0 && kr >= 0) {
+      PackZc<1> zk;
+      memset(&zk, 0, sizeof(zk));
+      zk.ctx[0] = c->ctx;
+      for (int q = 0; q < c->world; ++q) {
+        zk.z.send[q] = (const char*)c->regs[ks].peer[q] + offs;
+        zk.z.recv[q] = (char*)c->regs[kr].peer[q] + offr;
+      }
+      const u64 d[6] = {(u64)ks, offs, (u64)kr, offr, bytes, 1ull | ((u64)dtype << 8) | ((u64)op << 16)};
+      memcpy(zk.z.desc, d, sizeof(d));
+      OpParams prm = zc_params(c, bytes, op, 0);
+      c->last_algo = "ar_zerocopy";
+      return launch_zc_reduce<1>(Z_AR, dtype, op, pick_blocks(c, ceil_div(ceil_div(bytes, kUnit), c->world), 0), 1, s, zk,
+                                 &prm);
+    }
   }
   Plan p = plan_all_reduce(c, bytes, op, 0);
   Pack<1> pk;
@@ -692,6 +812,22 @@ int nbd_reduce_scatter(nbd_comm_t c, const void* send, void* recv, size_t recv_c
     if (send != recv) NBD_CUDA(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
     return NBD_OK;
   }
+  {
+    u64 offs = 0;
+    const int ks = zc_wanted(c, bytes) ? find_reg(c, send, bytes * c->world, &offs) : -1;
+    if (ks >= 0) {
+      PackZc<1> zk;
+      memset(&zk, 0, sizeof(zk));
+      zk.ctx[0] = c->ctx;
+      for (int q = 0; q < c->world; ++q) zk.z.send[q] = (const char*)c->regs[ks].peer[q] + offs;
+      zk.z.recv[c->rank] = (char*)recv;
+      const u64 d[6] = {(u64)ks, offs, 0, 0, bytes, 2ull | ((u64)dtype << 8) | ((u64)op << 16)};
+      memcpy(zk.z.desc, d, sizeof(d));
+      OpParams prm = zc_params(c, bytes, op, 0);
+      c->last_algo = "reduce_scatter_zerocopy";
+      return launch_zc_reduce<1>(Z_RS, dtype, op, pick_blocks(c, ceil_div(bytes, kUnit), 0), 1, s, zk, &prm);
+    }
+  }
   Plan p = plan_reduce_scatter(c, bytes, op, 0);
   Pack<1> pk;
   fill_pack(pk, c, send, recv);
@@ -713,6 +849,27 @@ int nbd_all_gather(nbd_comm_t c, const void* send, void* recv, size_t send_count
     c->last_algo = "local";
     if (send != recv) NBD_CUDA(cudaMemcpyAsync(recv, send, bytes, cudaMemcpyDeviceToDevice, s));
     return NBD_OK;
+  }
+  if (zc_wanted(c, bytes)) {
+    u64 offs = 0, offr = 0;
+    const int ks = find_reg(c, send, bytes, &offs);
+    const int kr = ks >= 0 ? -1 : find_reg(c, recv, bytes * c->world, &offr);
+    if (ks >= 0 || kr >= 0) {
+      PackZc<1> zk;
+      memset(&zk, 0, sizeof(zk));
+      zk.ctx[0] = c->ctx;
+      for (int q = 0; q < c->world; ++q) {
+        if (ks >= 0) zk.z.send[q] = (const char*)c->regs[ks].peer[q] + offs;
+        else zk.z.recv[q] = (char*)c->regs[kr].peer[q] + offr;
+      }
+      if (ks >= 0) zk.z.recv[c->rank] = (char*)recv;
+      else zk.z.send[c->rank] = (const char*)send;
+      const u64 d[6] = {(u64)(ks >= 0 ? ks : 0), offs, (u64)(kr >= 0 ? kr : 0), offr, bytes, 3ull | ((u64)(ks >= 0) << 8)};
+      memcpy(zk.z.desc, d, sizeof(d));
+      OpParams prm = zc_params(c, bytes, 0, ks >= 0 ? 0 : 1);
+      c->last_algo = ks >= 0 ? "all_gather_zerocopy_pull" : "all_gather_zerocopy_push";
+      return launch_ptr((const void*)k_all_gather_zc<1>, pick_blocks(c, ceil_div(bytes, kUnit), 0), 1, false, s, &zk, &prm);
+    }
   }
   Plan p = plan_all_gather(c, bytes, 0);
   Pack<1> pk;
@@ -786,6 +943,14 @@ int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* re
   cudaStream_t s = (cudaStream_t)stream;
   const u64 bytes = (u64)count * nbd_dtype_size(dtype);
   if (g->world == 1) return emu_local_copies(g, sends, recvs, bytes, s);
+  if (zc_wanted(c0, bytes)) {  // emulated ranks share one address space: always zero-copy capable
+    PackZc<kMaxRanks> zk;
+    if ((rc = fill_zc_emu(zk, g, sends, recvs)) != NBD_OK) return rc;
+    OpParams prm = zc_params(c0, bytes, op, 0);
+    set_algo(c0, "ar_zerocopy");
+    return launch_zc_reduce<kMaxRanks>(Z_AR, dtype, op, pick_blocks(c0, ceil_div(ceil_div(bytes, kUnit), g->world), g->world),
+                                       g->world, s, zk, &prm);
+  }
   Pack<kMaxRanks> pk;
   if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;
   Plan p = plan_all_reduce(c0, bytes, op, g->world);
@@ -805,9 +970,18 @@ int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends, void* const
   cudaStream_t s = (cudaStream_t)stream;
   const u64 bytes = (u64)recv_count * nbd_dtype_size(dtype);
   if (g->world == 1) return emu_local_copies(g, sends, recvs, bytes, s);
+  if (zc_wanted(c0, bytes)) {
+    PackZc<kMaxRanks> zk;
+    if ((rc = fill_zc_emu(zk, g, sends, recvs)) != NBD_OK) return rc;
+    OpParams prm = zc_params(c0, bytes, op, 0);
+    set_algo(c0, "reduce_scatter_zerocopy");
+    return launch_zc_reduce<kMaxRanks>(Z_RS, dtype, op, pick_blocks(c0, ceil_div(bytes, kUnit), g->world), g->world, s, zk,
+                                       &prm);
+  }
   Pack<kMaxRanks> pk;
   if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;
   Plan p = plan_reduce_scatter(c0, bytes, op, g->world);
+  for (int r = 1; r < g->world; ++r) g->comms[r]->last_algo = c0->last_algo;
   return launch_reduce<kMaxRanks>(K_RS, dtype, op, p.nblocks, g->world, s, pk, &p.op);
 }
 
@@ -824,9 +998,18 @@ int nbd_emu_all_gather(nbd_comm_t any, const void* const* sends, void* const* re
   cudaStream_t s = (cudaStream_t)stream;
   const u64 bytes = (u64)send_count * es;
   if (g->world == 1) return emu_local_copies(g, sends, recvs, bytes, s);
+  if (zc_wanted(c0, bytes)) {
+    PackZc<kMaxRanks> zk;
+    if ((rc = fill_zc_emu(zk, g, sends, recvs)) != NBD_OK) return rc;
+    OpParams prm = zc_params(c0, bytes, 0, 0);
+    set_algo(c0, "all_gather_zerocopy_pull");
+    return launch_ptr((const void*)k_all_gather_zc<kMaxRanks>, pick_blocks(c0, ceil_div(bytes, kUnit), g->world), g->world,
+                      true, s, &zk, &prm);
+  }
   Pack<kMaxRanks> pk;
   if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;
   Plan p = plan_all_gather(c0, bytes, g->world);
+  for (int r = 1; r < g->world; ++r) g->comms[r]->last_algo = c0->last_algo;
   return launch_any<kMaxRanks>((const void*)k_all_gather<kMaxRanks>, p.nblocks, g->world, s, pk, &p.op);
 }
 
@@ -989,4 +1172,95 @@ extern "C" int nbd_local_all_reduce_noalloc(const void* const* sends, void* cons
   // flags, clocks and mailboxes start from zero on every call (see the layout note above)
   NBD_CUDA(cudaMemsetAsync(base, 0, kNaCtlBytes, s));
   return launch_reduce<kMaxRanks>(p.op.algo == 1 ? K_AR1 : K_AR2, dtype, op, p.nblocks, world_size, s, pk, &p.op);
+}
+
+// ---------------------------------------------------------------------------
+// symmetric memory (see include/nbdist_b200.h)
+// ---------------------------------------------------------------------------
+extern "C" int nbd_mem_alloc(nbd_comm_t c, size_t bytes, void** ptr, void* handle_out) {
+  if (!c || !ptr || !handle_out) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL argument");
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "emulated ranks share one address space; no registration needed");
+  if (bytes == 0) return fail(NBD_ERR_INVALID_ARGUMENT, "cannot allocate 0 bytes");
+  DeviceGuard g(c->device);
+  const size_t rounded = (bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
+  char* base = nullptr;
+  NBD_CUDA(cudaMalloc((void**)&base, rounded));
+  Handle h;
+  memset(&h, 0, sizeof(h));
+  h.magic = kMagic;
+  h.version = NBD_VERSION;
+  h.rank = c->rank;
+  h.world = c->world;
+  h.pid = (int64_t)getpid();
+  h.hostid = host_id();
+  h.arena_bytes = rounded;
+  h.stage_bytes = (uint64_t)c->regs.size();  // allocation index: must match on every rank
+  if (c->world > 1) {
+    cudaError_t e = cudaIpcGetMemHandle(&h.ipc, base);
+    if (e != cudaSuccess) {
+      cudaFree(base);
+      cudaGetLastError();
+      return fail(NBD_ERR_CUDA, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+    }
+  }
+  nbd_comm::Registration reg;
+  reg.base = base;
+  reg.bytes = rounded;
+  reg.peer[c->rank] = base;
+  reg.connected = (c->world == 1);
+  c->regs.push_back(reg);
+  memset(handle_out, 0, NBD_HANDLE_BYTES);
+  memcpy(handle_out, &h, sizeof(h));
+  *ptr = base;
+  return NBD_OK;
+}
+
+extern "C" int nbd_mem_connect(nbd_comm_t c, void* ptr, const void* all_handles) {
+  if (!c || !ptr || !all_handles) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL argument");
+  int k = -1;
+  for (size_t i = 0; i < c->regs.size(); ++i)
+    if (c->regs[i].base == ptr) k = (int)i;
+  if (k < 0) return fail(NBD_ERR_INVALID_ARGUMENT, "pointer was not returned by nbd_mem_alloc on this communicator");
+  auto& reg = c->regs[(size_t)k];
+  if (reg.connected) return NBD_OK;
+  DeviceGuard g(c->device);
+  for (int p = 0; p < c->world; ++p) {
+    if (p == c->rank) continue;
+    Handle h;
+    memcpy(&h, (const char*)all_handles + (size_t)p * NBD_HANDLE_BYTES, sizeof(h));
+    if (h.magic != kMagic || h.rank != p || h.world != c->world)
+      return fail(NBD_ERR_INVALID_ARGUMENT, "memory handle %d is malformed", p);
+    if (h.stage_bytes != (uint64_t)k || h.arena_bytes != reg.bytes)
+      return fail(NBD_ERR_MISMATCH, "rank %d allocated buffer #%llu of %llu bytes, this rank #%d of %llu bytes: "
+                  "nbd_mem_alloc must be called in the same order with the same size on every rank", p,
+                  (unsigned long long)h.stage_bytes, (unsigned long long)h.arena_bytes, k, (unsigned long long)reg.bytes);
+    void* mapped = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&mapped, h.ipc, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(NBD_ERR_NO_PEER_ACCESS, "cudaIpcOpenMemHandle(buffer of rank %d): %s", p, cudaGetErrorString(e));
+    }
+    reg.peer[p] = mapped;
+  }
+  reg.connected = true;
+  return NBD_OK;
+}
+
+extern "C" int nbd_mem_free(nbd_comm_t c, void* ptr) {
+  if (!c || !ptr) return NBD_OK;
+  DeviceGuard g(c->device);
+  for (auto& reg : c->regs) {
+    if (reg.base != ptr) continue;
+    for (int p = 0; p < c->world; ++p)
+      if (p != c->rank && reg.peer[p]) {
+        cudaIpcCloseMemHandle(reg.peer[p]);
+        reg.peer[p] = nullptr;
+      }
+    cudaFree(reg.base);
+    reg.base = nullptr;  // the slot stays so that allocation indices remain aligned across ranks
+    reg.bytes = 0;
+    reg.connected = false;
+    return NBD_OK;
+  }
+  return fail(NBD_ERR_INVALID_ARGUMENT, "pointer was not returned by nbd_mem_alloc on this communicator");
 }

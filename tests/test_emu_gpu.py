@@ -43,6 +43,27 @@ def groups(torch_cuda):
         g.close()
 
 
+class tuned:
+    """Set tunables on a group for the duration of a with-block (0 restores the default)."""
+
+    def __init__(self, grp, **kv):
+        self.grp, self.kv = grp, kv
+
+    def __enter__(self):
+        for k, v in self.kv.items():
+            self.grp.set_tunable(k, v)
+        return self.grp
+
+    def __exit__(self, *exc):
+        for k in self.kv:
+            self.grp.set_tunable(k, 0)
+
+
+# staged = through the arena (what unregistered buffers of real ranks use);
+# zerocopy = straight between the ranks' buffers (registered memory; always possible when emulated)
+PATHS = {"staged": {"zero_copy_off": 1}, "zerocopy": {"zc_min_bytes": 1}}
+
+
 def _run_all_reduce(torch, grp, x, dtype, op="sum", inplace=True):
     sends = [H.to_cuda(a, dtype) for a in x]
     recvs = sends if inplace else [torch.empty_like(s) for s in sends]
@@ -52,15 +73,21 @@ def _run_all_reduce(torch, grp, x, dtype, op="sum", inplace=True):
     return [H.to_numpy(r, dtype) for r in recvs], [H.to_numpy(s, dtype) for s in sends]
 
 
+@pytest.mark.parametrize("path", ["staged", "zerocopy"])
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
 @pytest.mark.parametrize("dtype", ["f32", "bf16", "f16", "f64", "i32", "i64", "u8", "i8"])
 @pytest.mark.parametrize("numel", [1, 3, 127, 128, 1024, 4096 + 5, (1 << 18) + 1])
-def test_all_reduce_sum_matches_oracle(torch_cuda, groups, world, dtype, numel):
+def test_all_reduce_sum_matches_oracle(torch_cuda, groups, world, dtype, numel, path):
     x = O.make_inputs(world, numel, dtype)
-    got, _ = _run_all_reduce(torch_cuda, groups(world), x, dtype)
+    with tuned(groups(world), **PATHS[path]) as grp:
+        got, _ = _run_all_reduce(torch_cuda, grp, x, dtype)
+        assert (grp.last_algo() == "ar_zerocopy") == (path == "zerocopy")
+        got2, sends = _run_all_reduce(torch_cuda, grp, x, dtype, inplace=False)
     want = O.all_reduce(x, dtype, "sum", order="rank")
     for r in range(world):
         H.assert_same(got[r], want[r], dtype, f"rank {r}")
+        H.assert_same(got2[r], want[r], dtype, f"out of place, rank {r}")
+        H.assert_same(sends[r], x[r], dtype, f"send buffer of rank {r} was modified")
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -84,6 +111,7 @@ def test_all_reduce_two_shot_pipelined(torch_cuda, groups, world, numel, dtype):
     """Messages above the one-shot limit and above the 8 MiB staging: two-shot, several chunks."""
     grp = groups(world)
     grp.set_tunable("ar1_max_bytes", 1024)
+    grp.set_tunable("zero_copy_off", 1)
     try:
         x = O.make_inputs(world, numel, dtype)
         for inplace in (True, False):
@@ -96,6 +124,7 @@ def test_all_reduce_two_shot_pipelined(torch_cuda, groups, world, numel, dtype):
                     H.assert_same(sends[r], x[r], dtype, f"send buffer of rank {r} was modified")
     finally:
         grp.set_tunable("ar1_max_bytes", 0)
+        grp.set_tunable("zero_copy_off", 0)
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -103,6 +132,7 @@ def test_all_reduce_one_shot_pipelined(torch_cuda, groups, world):
     grp = groups(world)
     grp.set_tunable("ar1_max_bytes", 1 << 40)
     grp.set_tunable("chunk_bytes", 64 << 10)
+    grp.set_tunable("zero_copy_off", 1)
     try:
         x = O.make_inputs(world, (1 << 18) + 3, "f32")
         got, _ = _run_all_reduce(torch_cuda, grp, x, "f32")
@@ -113,6 +143,7 @@ def test_all_reduce_one_shot_pipelined(torch_cuda, groups, world):
     finally:
         grp.set_tunable("ar1_max_bytes", 0)
         grp.set_tunable("chunk_bytes", 0)
+        grp.set_tunable("zero_copy_off", 0)
 
 
 @pytest.mark.parametrize("dtype,op", [("f32", "prod"), ("f32", "min"), ("f32", "max"), ("f32", "avg"),
@@ -121,19 +152,18 @@ def test_all_reduce_one_shot_pipelined(torch_cuda, groups, world):
                                       ("i32", "bor"), ("i32", "bxor"), ("i64", "max"), ("i64", "bxor"),
                                       ("u8", "max"), ("u8", "min"), ("i8", "min"), ("i8", "max"), ("u8", "bor"),
                                       ("i8", "prod")])
-@pytest.mark.parametrize("twoshot", [False, True])
-def test_all_reduce_other_ops(torch_cuda, groups, dtype, op, twoshot):
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "zerocopy"])
+def test_all_reduce_other_ops(torch_cuda, groups, dtype, op, algo):
     world = 4
-    grp = groups(world)
-    grp.set_tunable("ar1_max_bytes", 1024 if twoshot else 0)
-    try:
+    knobs = {"oneshot": {"zero_copy_off": 1}, "twoshot": {"zero_copy_off": 1, "ar1_max_bytes": 1024},
+             "zerocopy": {"zc_min_bytes": 1}}[algo]
+    with tuned(groups(world), **knobs) as grp:
         x = O.make_inputs(world, 5000, dtype, scale=1.0)
         got, _ = _run_all_reduce(torch_cuda, grp, x, dtype, op=op)
+        assert grp.last_algo() == "ar_" + algo
         want = O.all_reduce(x, dtype, op)
         for r in range(world):
             H.assert_same(got[r], want[r], dtype, f"{op} rank {r}")
-    finally:
-        grp.set_tunable("ar1_max_bytes", 0)
 
 
 def test_all_reduce_special_values(torch_cuda, groups):
@@ -168,7 +198,9 @@ def test_all_reduce_misaligned_views(torch_cuda, groups):
     torch = torch_cuda
     world = 4
     grp = groups(world)
-    for dtype, off in (("f32", 1), ("bf16", 3), ("u8", 5), ("f64", 1)):
+    for zc, (dtype, off) in [(z, c) for z in (0, 1) for c in (("f32", 1), ("bf16", 3), ("u8", 5), ("f64", 1))]:
+        grp.set_tunable("zc_min_bytes", 1 if zc else 0)
+        grp.set_tunable("zero_copy_off", 0 if zc else 1)
         n = 3001
         x = O.make_inputs(world, n + off, dtype)
         full = [H.to_cuda(a, dtype) for a in x]
@@ -180,6 +212,8 @@ def test_all_reduce_misaligned_views(torch_cuda, groups):
         for r in range(world):
             H.assert_same(H.to_numpy(views[r], dtype), want[r], dtype, f"{dtype} rank {r}")
             H.assert_same(H.to_numpy(full[r][:off], dtype), x[r][:off], dtype, "bytes before the view were touched")
+    grp.set_tunable("zc_min_bytes", 0)
+    grp.set_tunable("zero_copy_off", 1)
     grp.set_tunable("ar1_max_bytes", 1024)
     try:
         x = O.make_inputs(world, 100003, "f32")
@@ -193,6 +227,7 @@ def test_all_reduce_misaligned_views(torch_cuda, groups):
             assert H.to_numpy(full[r], "f32")[0] == x[r][0] and H.to_numpy(full[r], "f32")[-1] == x[r][-1]
     finally:
         grp.set_tunable("ar1_max_bytes", 0)
+        grp.set_tunable("zero_copy_off", 0)
 
 
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
@@ -230,11 +265,14 @@ def test_broadcast_both_algorithms(torch_cuda, groups, world):
             grp.set_tunable("bcast_direct_max_bytes", 0)
 
 
+@pytest.mark.parametrize("path", ["staged", "zerocopy"])
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
 @pytest.mark.parametrize("dtype,numel", [("f32", 1), ("f32", 25), ("bf16", 4099), ("i64", 1 << 16), ("u8", (3 << 20) + 1)])
-def test_all_gather_bit_exact(torch_cuda, groups, world, dtype, numel):
+def test_all_gather_bit_exact(torch_cuda, groups, world, dtype, numel, path):
     torch = torch_cuda
     grp = groups(world)
+    for k, v in PATHS[path].items():
+        grp.set_tunable(k, v)
     x = O.make_inputs(world, numel, dtype)
     sends = [H.to_cuda(a, dtype) for a in x]
     recvs = [torch.zeros(world * numel, dtype=sends[0].dtype, device="cuda:0") for _ in range(world)]
@@ -250,21 +288,30 @@ def test_all_gather_bit_exact(torch_cuda, groups, world, dtype, numel):
         recvs2[r][r * numel:(r + 1) * numel].copy_(sends[r])
     grp.all_gather([recvs2[r][r * numel:(r + 1) * numel] for r in range(world)], recvs2)
     torch.cuda.synchronize()
+    assert grp.last_algo() == ("all_gather_zerocopy_pull" if path == "zerocopy" else "all_gather_pull")
+    for k in PATHS[path]:
+        grp.set_tunable(k, 0)
     for r in range(world):
         H.assert_same(H.to_numpy(recvs2[r], dtype), want[r], dtype, f"in-place rank {r}")
 
 
+@pytest.mark.parametrize("path", ["staged", "zerocopy"])
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
 @pytest.mark.parametrize("dtype,numel", [("f32", 1), ("f32", 1001), ("bf16", 4099), ("i32", 1 << 15), ("bf16", (1 << 20) + 8)])
-def test_reduce_scatter_matches_oracle(torch_cuda, groups, world, dtype, numel):
+def test_reduce_scatter_matches_oracle(torch_cuda, groups, world, dtype, numel, path):
     torch = torch_cuda
     grp = groups(world)
+    for k, v in PATHS[path].items():
+        grp.set_tunable(k, v)
     x = O.make_inputs(world, world * numel, dtype)
     sends = [H.to_cuda(a, dtype) for a in x]
     recvs = [torch.zeros(numel, dtype=sends[0].dtype, device="cuda:0") for _ in range(world)]
     grp.reduce_scatter(sends, recvs)
     torch.cuda.synchronize()
     grp.async_error()
+    assert grp.last_algo() == ("reduce_scatter_zerocopy" if path == "zerocopy" else "reduce_scatter_push")
+    for k in PATHS[path]:
+        grp.set_tunable(k, 0)
     want = O.reduce_scatter(x, dtype, "sum")
     for r in range(world):
         H.assert_same(H.to_numpy(recvs[r], dtype), want[r], dtype, f"rank {r}")
@@ -355,13 +402,17 @@ def test_large_all_reduce_properties(torch_cuda):
             g.manual_seed(1234 + r)
             t.append(torch.randint(-1000, 1000, (numel,), generator=g, device="cuda:0", dtype=torch.int32).to(torch.float32))
         keep = [a.clone() for a in t]
-        grp.all_reduce(t, t)
-        torch.cuda.synchronize()
-        grp.async_error()
-        assert grp.last_algo() == "ar_twoshot"
         want = keep[0] + keep[1] + keep[2] + keep[3]  # small integers: exact in fp32 in any order
-        for r in range(world):
-            assert torch.equal(t[r], want), f"rank {r}"
+        for off, algo in ((1, "ar_twoshot"), (0, "ar_zerocopy")):
+            grp.set_tunable("zero_copy_off", off)
+            for r in range(world):
+                t[r].copy_(keep[r])
+            grp.all_reduce(t, t)
+            torch.cuda.synchronize()
+            grp.async_error()
+            assert grp.last_algo() == algo
+            for r in range(world):
+                assert torch.equal(t[r], want), f"{algo} rank {r}"
         idx = np.random.default_rng(0).integers(0, numel, 4096)
         sample = [H.to_numpy(k[idx], "f32") for k in keep]
         H.assert_same(H.to_numpy(t[0][idx], "f32"), O.reduce_rank_order(sample, "f32"), "f32")

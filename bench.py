@@ -425,6 +425,8 @@ def run_ours_multi(args):
     if not args.no_sweep:
         log("message-size sweep")
         extras["sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be)
+        log("registered-memory sweep")
+        extras["registered"] = registered_sweep(torch, dist, dev, world, cpu_group, be)
     if not args.no_nccl:
         log("NCCL comparison point")
         extras["nccl"] = nccl_comparison(torch, dist, dev, world, cpu_group, S)
@@ -461,8 +463,43 @@ def run_ours_multi(args):
     return line
 
 
+def registered_sweep(torch, dist, dev, world, cpu_group, be):
+    """The same collectives on symmetric memory (Backend.allocate_tensor): zero-copy kernels."""
+    from nbdistributed_b200 import backend as B
+
+    out = []
+    big = B.empty_symmetric((1 << 30) // 4, torch.float32)
+    for nbytes in (1 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30):
+        buf = big[: nbytes // 4]
+        buf.fill_(1.0)
+        iters = 50 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 5)
+        ms = _time_collective(torch, dist, lambda: dist.all_reduce(buf), iters, 3, cpu_group)
+        out.append({"op": "all_reduce", "dtype": "float32", "bytes": nbytes, "us": round(ms * 1e3, 2),
+                    "busbw_per_rank": round(nbytes * bus_factor(world) / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
+    # ZeRO-style pair on a flat bf16 buffer (BASELINE config 5, scaled to 1 GiB total)
+    flat = big.view(torch.bfloat16)[: (1 << 30) // 2]
+    shard = torch.empty(flat.numel() // world, dtype=torch.bfloat16, device=dev)
+    flat.fill_(0.01)
+    for name, fn in (("reduce_scatter", lambda: dist.reduce_scatter_tensor(shard, flat)),
+                     ("all_gather", lambda: dist.all_gather_into_tensor(flat, shard))):
+        ms = _time_collective(torch, dist, fn, 5, 2, cpu_group)
+        out.append({"op": name, "dtype": "bfloat16", "bytes": 1 << 30, "us": round(ms * 1e3, 2),
+                    "busbw_per_rank": round((1 << 30) * (world - 1) / world / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
+    del flat, big
+    return out
+
+
 def multi_sweep(torch, dist, dev, world, cpu_group, be):
     out = []
+    # ZeRO-style pair on ordinary tensors (BASELINE config 5, scaled to 1 GiB total)
+    flat = torch.full(((1 << 30) // 2,), 0.01, device=dev, dtype=torch.bfloat16)
+    shard = torch.empty(flat.numel() // world, dtype=torch.bfloat16, device=dev)
+    for name, fn in (("reduce_scatter", lambda: dist.reduce_scatter_tensor(shard, flat)),
+                     ("all_gather", lambda: dist.all_gather_into_tensor(flat, shard))):
+        ms = _time_collective(torch, dist, fn, 5, 2, cpu_group)
+        out.append({"op": name, "dtype": "bfloat16", "bytes": 1 << 30, "us": round(ms * 1e3, 2),
+                    "busbw_per_rank": round((1 << 30) * (world - 1) / world / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
+    del flat, shard
     for kind in ("all_reduce", "broadcast"):
         for dt, es in ((torch.float32, 4), (torch.bfloat16, 2)):
             for nbytes in (4 << 10, 64 << 10, 1 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30):

@@ -63,6 +63,18 @@ def get_backend(group=None):
     return pg._get_backend(torch.device("cuda"))
 
 
+def empty_symmetric(numel: int, dtype=None, group=None):
+    """A 1-D CUDA tensor in symmetric memory (mapped by every rank of ``group``): collectives on
+    it — or on views of it, at the same offset on every rank — run zero-copy over NVLink instead
+    of through the staging arena.  COLLECTIVE: every rank must call it in the same order with
+    the same size (it is ``Backend.allocate_tensor``, which FSDP also uses).  Keep the process
+    group alive for as long as the tensor is used."""
+    import torch
+
+    be = get_backend(group)
+    return be.allocate_tensor(int(numel), dtype=dtype or torch.float32, device=torch.device("cuda", torch.cuda.current_device()))
+
+
 def launch_count() -> int:
     """Kernels launched by the native library in this process (bench.py's gpu_launches)."""
     return int(_load_ext().launch_count())

@@ -20,11 +20,13 @@
 #include <torch/csrc/distributed/c10d/Types.hpp>
 #include <torch/csrc/distributed/c10d/Work.hpp>
 #include <torch/extension.h>
+#include <ATen/ops/from_blob.h>
 
 #include <execinfo.h>
 #include <signal.h>
 #include <unistd.h>
 
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -213,6 +215,7 @@ class BackendB200 : public c10d::Backend {
         // store already gone (rank 0 exited or peers were killed): nothing to wait for
       }
     }
+    alive_->store(false);
     nbd_comm_destroy(comm_);
     comm_ = nullptr;
     comm_stream_.reset();
@@ -399,6 +402,43 @@ class BackendB200 : public c10d::Backend {
                [&](cudaStream_t s) { return nbd_barrier(comm_, s); });
   }
 
+  // ---- symmetric memory: Backend::allocateTensor ($TORCH/.../Backend.hpp:492-503) -------
+  // Collective (every rank, same order, same size), like ncclMemAlloc + window registration.
+  // Tensors obtained here are mapped by every peer; collectives on them skip the staging arena.
+  bool supportsTensorAlloc(c10::DeviceIndex /*deviceIdx*/) override { return true; }
+
+  at::Tensor allocateTensor(long size, at::TensorOptions options = {}) override {
+    TORCH_CHECK(size > 0, "[b200] allocateTensor needs a positive element count");
+    c10::DeviceIndex dev = options.has_device() && options.device().has_index() ? options.device().index()
+                                                                               : (comm_ ? device_ : c10::cuda::current_device());
+    std::lock_guard<std::mutex> lk(mu_);
+    ensure_comm(dev);
+    c10::cuda::CUDAGuard g(dev);
+    const auto dtype = options.has_dtype() ? c10::typeMetaToScalarType(options.dtype()) : at::kFloat;
+    const size_t bytes = (size_t)size * c10::elementSize(dtype);
+    void* ptr = nullptr;
+    std::vector<uint8_t> mine(NBD_HANDLE_BYTES);
+    NBD_CHECK(nbd_mem_alloc(comm_, bytes, &ptr, mine.data()), "nbd_mem_alloc");
+    const int idx = mem_seq_++;
+    if (getSize() > 1) {
+      store_->set(c10::str("nbd_b200/mem/", idx, "/", getRank()), mine);
+      std::vector<uint8_t> all((size_t)getSize() * NBD_HANDLE_BYTES);
+      for (int r = 0; r < getSize(); ++r) {
+        std::vector<uint8_t> h = (r == getRank()) ? mine : store_->get(c10::str("nbd_b200/mem/", idx, "/", r));
+        TORCH_CHECK(h.size() == NBD_HANDLE_BYTES, "[b200] malformed memory handle from rank ", r);
+        std::memcpy(all.data() + (size_t)r * NBD_HANDLE_BYTES, h.data(), NBD_HANDLE_BYTES);
+      }
+      NBD_CHECK(nbd_mem_connect(comm_, ptr, all.data()), "nbd_mem_connect");
+    }
+    auto alive = alive_;
+    nbd_comm_t comm = comm_;
+    auto deleter = [alive, comm](void* p) {
+      if (alive->load()) nbd_mem_free(comm, p);  // after shutdown the communicator already freed it
+    };
+    return at::from_blob(ptr, {(int64_t)size}, deleter,
+                         at::TensorOptions().dtype(dtype).device(c10::Device(c10::kCUDA, dev)));
+  }
+
   // ---- extras exposed to Python ------------------------------------------------
   void set_tunable(const std::string& name, uint64_t value) {
     tunables_.emplace_back(name, value);
@@ -513,6 +553,8 @@ class BackendB200 : public c10d::Backend {
   std::optional<c10::cuda::CUDAStream> last_stream_;
   bool has_last_ = false;
   bool inline_sync_ops_ = true;
+  int mem_seq_ = 0;
+  std::shared_ptr<std::atomic<bool>> alive_ = std::make_shared<std::atomic<bool>>(true);
   std::vector<std::pair<std::string, uint64_t>> tunables_;
 };
 

@@ -114,6 +114,50 @@ def body(rank: int, world: int, port: int) -> None:
         dist.reduce_scatter(o2, list(s.chunk(world)))
         assert torch.equal(o, o2), "reduce_scatter list form differs from tensor form"
 
+    # ---- symmetric memory (Backend.allocate_tensor): zero-copy kernels over NVLink ----------
+    assert be.supports_tensor_alloc(dev)
+    n_sym = (6 << 20) + 64
+    sym = B.empty_symmetric(n_sym, torch.float32)
+    sym2 = B.empty_symmetric(n_sym, torch.bfloat16)
+    assert sym.is_cuda and sym.numel() == n_sym and sym2.dtype == torch.bfloat16
+    for numel, off in ((n_sym, 0), ((1 << 20) + 3, 16), (70001, 4 * 999)):
+        x = O.make_inputs(world, numel, "f32", seed=21)
+        v = sym[off:off + numel]
+        v.copy_(H.to_cuda(x[rank], "f32", dev))
+        dist.all_reduce(v)
+        expect_zc = numel * 4 >= (256 << 10)
+        assert (be.last_algo() == "ar_zerocopy") == expect_zc, be.last_algo()
+        H.assert_same(_np(v, "f32"), O.reduce_rank_order(x, "f32"), "f32", f"zero-copy all_reduce n={numel} off={off}")
+    x = O.make_inputs(world, 1 << 20, "bf16", seed=22)
+    v = sym2[: 1 << 20]
+    v.copy_(H.to_cuda(x[rank], "bf16", dev))
+    dist.all_reduce(v, op=dist.ReduceOp.MAX)
+    assert be.last_algo() == "ar_zerocopy"
+    H.assert_same(_np(v, "bf16"), O.reduce_rank_order(x, "bf16", "max"), "bf16", "zero-copy all_reduce max bf16")
+    shard = (1 << 19) + 16
+    xs = O.make_inputs(world, world * shard, "f32", seed=23)
+    sym[: world * shard].copy_(H.to_cuda(xs[rank], "f32", dev))
+    o = torch.empty(shard, dtype=torch.float32, device=dev)
+    dist.reduce_scatter_tensor(o, sym[: world * shard])          # send registered
+    assert be.last_algo() == "reduce_scatter_zerocopy", be.last_algo()
+    H.assert_same(_np(o, "f32"), O.reduce_scatter(xs, "f32")[rank], "f32", "zero-copy reduce_scatter")
+    full = torch.empty(world * shard, dtype=torch.float32, device=dev)
+    dist.all_gather_into_tensor(full, sym[:shard])                # send registered -> pull
+    assert be.last_algo() == "all_gather_zerocopy_pull", be.last_algo()
+    want_ag = np.concatenate([a[:shard] for a in xs])
+    H.assert_same(_np(full, "f32"), want_ag, "f32", "zero-copy all_gather (pull)")
+    src = H.to_cuda(xs[rank][:shard], "f32", dev)
+    dist.all_gather_into_tensor(sym[: world * shard], src)        # recv registered -> push
+    assert be.last_algo() == "all_gather_zerocopy_push", be.last_algo()
+    H.assert_same(_np(sym[: world * shard], "f32"), want_ag, "f32", "zero-copy all_gather (push)")
+    # staged and zero-copy collectives interleave freely on one communicator
+    y = H.to_cuda(xs[rank][:shard], "f32", dev)
+    dist.all_reduce(y)
+    dist.all_reduce(sym[:shard])
+    dist.all_reduce(y)
+    torch.cuda.synchronize()
+    del sym, sym2
+
     # ---- async ops, futures, barrier, non-contiguous rejection -----------------------------
     x = O.make_inputs(world, 1 << 20, "f32", seed=3)
     t = H.to_cuda(x[rank], "f32", dev)

@@ -226,6 +226,14 @@ int nbd_local_all_reduce_noalloc(const void* const* sends, void* const* recvs, i
 
 /* Number of kernels this library has launched in this process so far. */
 uint64_t nbd_launch_count(void);
+/* Ordinary (unregistered) buffers of at least "auto_min_bytes" (tunable, default 8 MiB) are
+ * registered on the fly: the allocation is exported through CUDA IPC on first use, peers import
+ * it lazily, and a one-CTA kernel agrees per operation whether every rank can address every
+ * rank's buffers; if so the zero-copy kernel runs, otherwise the staged one (both are
+ * enqueued, the decision gates them).  Returns 1 if the most recent such collective ran
+ * zero-copy, 0 if staged.  Synchronises the device: diagnostics and tests only.
+ * "auto_register_off" = 1 (or NBDIST_B200_AUTO_REGISTER=0) disables the mechanism. */
+int nbd_comm_last_zc_decision(nbd_comm_t comm);
 /* Name of the algorithm the last collective on `comm` used
  * ("ar_oneshot", "ar_twoshot", "bcast_direct", "bcast_scatter", ...). */
 const char* nbd_last_algo(nbd_comm_t comm);

@@ -36,6 +36,7 @@ SYMBOLS = [
     "nbd_all_reduce", "nbd_broadcast", "nbd_all_gather", "nbd_reduce_scatter", "nbd_barrier",
     "nbd_emu_all_reduce", "nbd_emu_broadcast", "nbd_emu_all_gather", "nbd_emu_reduce_scatter", "nbd_emu_barrier",
     "nbd_local_all_reduce_noalloc",
+    "nbd_comm_last_zc_decision",
     "nbd_launch_count", "nbd_last_algo",
 ]
 NOALLOC_MAX_BYTES = 1 << 20
@@ -94,6 +95,7 @@ def load() -> C.CDLL:
         "nbd_emu_reduce_scatter": (i, [vp, pp, pp, sz, i, i, vp]),
         "nbd_emu_barrier": (i, [vp, vp]),
         "nbd_local_all_reduce_noalloc": (i, [pp, pp, i, sz, i, i, vp]),
+        "nbd_comm_last_zc_decision": (i, [vp]),
         "nbd_launch_count": (u64, []),
         "nbd_last_algo": (C.c_char_p, [vp]),
     }

@@ -445,6 +445,7 @@ class BackendB200 : public c10d::Backend {
     if (comm_) NBD_CHECK(nbd_comm_set_tunable(comm_, name.c_str(), value), "set_tunable");
   }
   std::string last_algo() { return comm_ ? nbd_last_algo(comm_) : "none"; }
+  int last_zc_decision() { return comm_ ? nbd_comm_last_zc_decision(comm_) : -1; }
   int64_t device_index() const { return comm_ ? (int64_t)device_ : -1; }
   void set_inline_sync_ops(bool v) { inline_sync_ops_ = v; }
 
@@ -571,6 +572,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   py::class_<BackendB200, c10::intrusive_ptr<BackendB200>, c10d::Backend>(m, "BackendB200")
       .def("set_tunable", &BackendB200::set_tunable)
       .def("last_algo", &BackendB200::last_algo)
+      .def("last_zc_decision", &BackendB200::last_zc_decision)
       .def("device_index", &BackendB200::device_index)
       .def("set_inline_sync_ops", &BackendB200::set_inline_sync_ops);
   m.def("create_backend", &create_backend, py::arg("store"), py::arg("rank"), py::arg("size"), py::arg("timeout"),

@@ -39,9 +39,13 @@ struct LocalState {
 };
 
 // Pinned host memory, visible to the device: async error reporting + abort.
+constexpr int kMissRing = 24;
 struct HostMailbox {
   u32 error;  // 0, or -nbd_result set by a kernel (timeout / abort)
   u32 abort;  // host sets to 1 to make flag waits give up
+  u32 miss_count;        // auto-registration: number of (peer, export slot) pairs reported so far
+  u32 pad;
+  u64 miss[kMissRing];   // ring of (peer << 32 | slot) this rank has not imported yet
 };
 
 struct RankCtx {
@@ -84,6 +88,40 @@ struct PackZc {
   ZcPtrs z;
 };
 
+// Auto-registration (ordinary, unregistered tensors): each rank exports the allocations its
+// tensors live in (CUDA IPC) into EXPORT SLOTS of its arena, peers import them lazily.  Before
+// an eligible collective a one-CTA kernel (k_zc_agree) exchanges {slot, offset} descriptors,
+// resolves them through the local import table and agrees, across ranks, whether everybody
+// can address everybody's buffers.  The zero-copy kernel and the staged kernel are then both
+// enqueued; each returns at once if the decision is not for it.
+constexpr int kExportRow0 = 512;                       // export slots use flag rows [512, 1008)
+constexpr int kExportSlotRows = 2;                     // 2 rows x 64 B = 128 B per slot
+constexpr int kMaxExports = (kMaxBlocks - 2 * kMaxRanks - kExportRow0) / kExportSlotRows;  // 248
+constexpr u64 kNoSlot = ~0ull;
+
+struct ExportSlot {   // 128 B, written by the exporting rank's host, read by peers' hosts
+  u64 buffer_id;      // CU_POINTER_ATTRIBUTE_BUFFER_ID of the allocation (unique per allocation)
+  u64 base;
+  u64 size;
+  u64 valid;          // 1 once the record is complete
+  unsigned char ipc[64];
+  u64 pad[4];
+};
+
+struct ZcDecision {
+  u32 ok;             // 1: every rank can address every rank's buffers of the pending operation
+  u32 pad;
+  ZcPtrs z;
+};
+
+// Rank-private device block; LocalState stays first so that RankCtx::state needs no change.
+struct LocalBlock {
+  LocalState st;
+  ZcDecision dec;
+  u64 imp[kMaxRanks][kMaxExports];  // imp[p][slot]: rank p's exported allocation mapped here, or 0
+  u64 prev_desc[kMaxRanks][6];      // every rank's descriptor of the previous agreement
+};
+
 // Operation descriptors for the symmetric-use check live in flag rows no grid ever reaches
 // (grids are capped well below kDescRow CTAs): row kDescRow + src holds rank src's 8 words.
 constexpr int kDescRow = kMaxBlocks - 2 * kMaxRanks;
@@ -98,6 +136,8 @@ struct OpParams {
   int algo;         // kernel-specific variant
   int world;
   int avg;          // 1: divide the sum by world (NBD_AVG)
+  int zc_mode;      // 0: unconditional; 1: zero-copy kernel, run only if the agreed decision is ok
+                    // (buffers come from the decision); 2: staged kernel, run only if it is not
 };
 
 // ---------------------------------------------------------------------------

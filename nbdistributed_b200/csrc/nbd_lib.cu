@@ -5,6 +5,7 @@
 //
 // Replaces, for one NVLink/NVSwitch node, the transport that torch's "nccl"
 // backend provides behind ref:src/nbdistributed/worker.py:151.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -14,6 +15,8 @@
 
 #include <atomic>
 #include <mutex>
+#include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -82,6 +85,19 @@ struct nbd_comm {
     bool connected = false;
   };
   std::vector<Registration> regs;
+  // auto-registration of ordinary allocations (exports: ours; imports: peers')
+  uint64_t t_auto_off = 0, t_auto_min = 0;
+  ExportSlot* export_mirror = nullptr;          // pinned host copy of our export slots
+  int n_exports = 0;
+  std::map<uint64_t, int> export_of;            // buffer id -> slot
+  std::set<uint64_t> not_exportable;            // buffer ids cudaIpcGetMemHandle refused
+  std::set<uint64_t> imported;                  // (peer << 32 | slot) already mapped
+  std::vector<void*> import_ptrs;               // mappings to close at destroy
+  uint32_t miss_seen = 0;
+  cudaStream_t side = nullptr;                  // for reading peers' export slots
+  ExportSlot* import_tmp = nullptr;             // pinned scratch for one slot
+  uint64_t* imp_tmp = nullptr;                  // pinned ring of pointers handed to cudaMemcpyAsync
+  int imp_tmp_n = 0;
   uint64_t timeout_ms = 600000;
   const char* last_algo = "none";
 };
@@ -135,11 +151,17 @@ static int alloc_rank(nbd_comm* c, size_t stage_bytes) {
   c->num_sms = prop.multiProcessorCount;
   NBD_CUDA(cudaMalloc((void**)&c->arena, c->arena_bytes));
   NBD_CUDA(cudaMemset(c->arena, 0, kFlagBytes));
-  NBD_CUDA(cudaMalloc((void**)&c->state, sizeof(LocalState)));
-  NBD_CUDA(cudaMemset(c->state, 0, sizeof(LocalState)));
+  NBD_CUDA(cudaMalloc((void**)&c->state, sizeof(LocalBlock)));  // LocalState is its first member
+  NBD_CUDA(cudaMemset(c->state, 0, sizeof(LocalBlock)));
+  if (!c->emu) {
+    NBD_CUDA(cudaHostAlloc((void**)&c->export_mirror, sizeof(ExportSlot) * kMaxExports, cudaHostAllocPortable));
+    memset(c->export_mirror, 0, sizeof(ExportSlot) * kMaxExports);
+    NBD_CUDA(cudaHostAlloc((void**)&c->import_tmp, sizeof(ExportSlot), cudaHostAllocPortable));
+    NBD_CUDA(cudaHostAlloc((void**)&c->imp_tmp, sizeof(uint64_t) * 64, cudaHostAllocPortable));
+    NBD_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+  }
   NBD_CUDA(cudaHostAlloc((void**)&c->mbox, sizeof(HostMailbox), cudaHostAllocMapped | cudaHostAllocPortable));
-  c->mbox->error = 0;
-  c->mbox->abort = 0;
+  memset(c->mbox, 0, sizeof(HostMailbox));
   NBD_CUDA(cudaHostGetDevicePointer((void**)&c->mbox_dev, c->mbox, 0));
   NBD_CUDA(cudaDeviceSynchronize());
   const char* t = getenv("NBDIST_B200_TIMEOUT_MS");
@@ -152,6 +174,10 @@ static int alloc_rank(nbd_comm* c, size_t stage_bytes) {
   if (a1) c->t_ar1_max = strtoull(a1, nullptr, 0);
   const char* bd = getenv("NBDIST_B200_BCAST_DIRECT_MAX_BYTES");
   if (bd) c->t_bcast_direct_max = strtoull(bd, nullptr, 0);
+  const char* ao = getenv("NBDIST_B200_AUTO_REGISTER");
+  if (ao && ao[0] == '0') c->t_auto_off = 1;
+  const char* am = getenv("NBDIST_B200_AUTO_MIN_BYTES");
+  if (am) c->t_auto_min = strtoull(am, nullptr, 0);
   return NBD_OK;
 }
 
@@ -183,6 +209,12 @@ static void free_rank(nbd_comm* c) {
     if (g.base) cudaFree(g.base);
   }
   c->regs.clear();
+  for (void* m : c->import_ptrs) cudaIpcCloseMemHandle(m);
+  c->import_ptrs.clear();
+  if (c->side) cudaStreamDestroy(c->side);
+  if (c->export_mirror) cudaFreeHost(c->export_mirror);
+  if (c->import_tmp) cudaFreeHost(c->import_tmp);
+  if (c->imp_tmp) cudaFreeHost(c->imp_tmp);
   if (c->arena) cudaFree(c->arena);
   if (c->state) cudaFree(c->state);
   if (c->mbox) cudaFreeHost(c->mbox);
@@ -354,6 +386,8 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "chunk_bytes")) return &c->t_chunk;
   if (!strcmp(name, "zero_copy_off")) return &c->t_zc_off;
   if (!strcmp(name, "zc_min_bytes")) return &c->t_zc_min;
+  if (!strcmp(name, "auto_register_off")) return &c->t_auto_off;
+  if (!strcmp(name, "auto_min_bytes")) return &c->t_auto_min;
   return nullptr;
 }
 
@@ -452,7 +486,7 @@ static int pick_blocks(const nbd_comm* c, u64 units_per_block_span, int emu_worl
   u64 cap = (u64)c->num_sms * kMinBlocksPerSM;
   if (emu_world > 1) cap /= (u64)emu_world;
   if (c->t_blocks && c->t_blocks < cap) cap = c->t_blocks;
-  if (cap > (u64)kDescRow) cap = kDescRow;
+  if (cap > (u64)kExportRow0) cap = kExportRow0;  // rows above hold export slots and descriptors
   if (cap < 1) cap = 1;
   u64 want = ceil_div(units_per_block_span, (u64)kThreads * 4);
   if (want < 1) want = 1;
@@ -751,6 +785,138 @@ static void set_algo(nbd_comm* c, const char* name) {
     for (int r = 0; r < c->group->world; ++r) c->group->comms[r]->last_algo = name;
 }
 
+
+// ---------------------------------------------------------------------------
+// auto-registration of ordinary (unregistered) buffers — see nbd_device.cuh
+// ---------------------------------------------------------------------------
+static const u64 kDefAutoMin = 8ull << 20;
+
+typedef CUresult (*PFN_cuPointerGetAttribute)(void*, CUpointer_attribute, CUdeviceptr);
+typedef CUresult (*PFN_cuMemGetAddressRange)(CUdeviceptr*, size_t*, CUdeviceptr);
+static PFN_cuPointerGetAttribute p_cuPointerGetAttribute = nullptr;
+static PFN_cuMemGetAddressRange p_cuMemGetAddressRange = nullptr;
+static std::once_flag g_drv_once;
+
+static void load_driver_entry_points() {
+  std::call_once(g_drv_once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &f, cudaEnableDefault, &q) == cudaSuccess && f)
+      p_cuPointerGetAttribute = (PFN_cuPointerGetAttribute)f;
+    f = nullptr;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &q) == cudaSuccess && f)
+      p_cuMemGetAddressRange = (PFN_cuMemGetAddressRange)f;
+    cudaGetLastError();
+  });
+}
+
+static bool auto_wanted(const nbd_comm* c, u64 bytes) {
+  return !c->emu && c->world > 1 && !c->t_zc_off && !c->t_auto_off &&
+         bytes >= (c->t_auto_min ? c->t_auto_min : kDefAutoMin);
+}
+
+struct ExportRef {
+  u64 slot = kNoSlot;
+  u64 off = 0;
+};
+
+// The export slot of the allocation that holds [ptr, ptr+bytes), exporting it on first use.
+// kNoSlot when the allocation cannot be shared (not a cudaMalloc allocation, table full, ...).
+static ExportRef export_ref(nbd_comm* c, const void* ptr, u64 bytes, cudaStream_t s) {
+  ExportRef ref;
+  load_driver_entry_points();
+  if (!p_cuPointerGetAttribute || !p_cuMemGetAddressRange) return ref;
+  unsigned long long id = 0;
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  if (p_cuPointerGetAttribute(&id, CU_POINTER_ATTRIBUTE_BUFFER_ID, (CUdeviceptr)ptr) != CUDA_SUCCESS) return ref;
+  if (p_cuMemGetAddressRange(&base, &size, (CUdeviceptr)ptr) != CUDA_SUCCESS) return ref;
+  if ((CUdeviceptr)ptr + bytes > base + size) return ref;
+  auto it = c->export_of.find(id);
+  if (it == c->export_of.end()) {
+    if (c->not_exportable.count(id) || c->n_exports >= kMaxExports) return ref;
+    ExportSlot& e = c->export_mirror[c->n_exports];
+    memset(&e, 0, sizeof(e));
+    cudaIpcMemHandle_t h;
+    if (cudaIpcGetMemHandle(&h, (void*)base) != cudaSuccess) {
+      cudaGetLastError();
+      c->not_exportable.insert(id);  // e.g. expandable (VMM) segments of torch's allocator
+      return ref;
+    }
+    e.buffer_id = id;
+    e.base = (u64)base;
+    e.size = (u64)size;
+    memcpy(e.ipc, &h, sizeof(h));
+    e.valid = 1;
+    char* row = c->arena + (size_t)(kExportRow0 + c->n_exports * kExportSlotRows) * kMaxRanks * sizeof(u64);
+    if (cudaMemcpyAsync(row, &e, sizeof(e), cudaMemcpyHostToDevice, s) != cudaSuccess) {
+      cudaGetLastError();
+      return ref;
+    }
+    it = c->export_of.emplace(id, c->n_exports++).first;
+  }
+  ref.slot = (u64)it->second;
+  ref.off = (u64)((CUdeviceptr)ptr - (CUdeviceptr)c->export_mirror[it->second].base);
+  return ref;
+}
+
+// Import the (peer, slot) pairs kernels reported as unresolved; later operations on those
+// allocations run zero-copy.  Failures are remembered and simply keep the staged path.
+static void process_misses(nbd_comm* c, cudaStream_t s) {
+  const uint32_t count = ((volatile HostMailbox*)c->mbox)->miss_count;
+  if (count == c->miss_seen) return;
+  uint32_t first = c->miss_seen;
+  if (count - first > (uint32_t)kMissRing) first = count - kMissRing;
+  c->miss_seen = count;
+  LocalBlock* blk = reinterpret_cast<LocalBlock*>(c->state);
+  for (uint32_t i = first; i != count; ++i) {
+    const u64 key = ((volatile HostMailbox*)c->mbox)->miss[i % kMissRing];
+    const int peer = (int)(key >> 32);
+    const u64 slot = key & 0xffffffffull;
+    if (peer < 0 || peer >= c->world || peer == c->rank || slot >= (u64)kMaxExports) continue;
+    if (!c->imported.insert(key).second) continue;
+    const char* row = (const char*)c->peer_base[peer] + (size_t)(kExportRow0 + slot * kExportSlotRows) * kMaxRanks * sizeof(u64);
+    if (cudaMemcpyAsync(c->import_tmp, row, sizeof(ExportSlot), cudaMemcpyDeviceToHost, c->side) != cudaSuccess ||
+        cudaStreamSynchronize(c->side) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    if (c->import_tmp->valid != 1) {
+      c->imported.erase(key);  // not published yet: try again when it is reported again
+      continue;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, c->import_tmp->ipc, sizeof(h));
+    void* mapped = nullptr;
+    if (cudaIpcOpenMemHandle(&mapped, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    c->import_ptrs.push_back(mapped);
+    uint64_t* cell = &c->imp_tmp[c->imp_tmp_n++ % 64];
+    *cell = (uint64_t)mapped;
+    if (cudaMemcpyAsync(&blk->imp[peer][slot], cell, sizeof(uint64_t), cudaMemcpyHostToDevice, s) != cudaSuccess)
+      cudaGetLastError();
+  }
+}
+
+static int launch_agree(nbd_comm* c, const ExportRef& es, const ExportRef& er, u64 bytes, u64 optag, int need,
+                        const void* send, void* recv, cudaStream_t s) {
+  Pack<1> pk;
+  fill_pack(pk, c, send, recv);
+  AgreeArgs a;
+  memset(&a, 0, sizeof(a));
+  const u64 d[6] = {es.slot, es.off, er.slot, er.off, bytes, optag};
+  memcpy(a.desc, d, sizeof(d));
+  a.local_send = (const char*)send;
+  a.local_recv = (char*)recv;
+  a.need = need;
+  void* args[2] = {(void*)&pk, (void*)&a};
+  NBD_CUDA(cudaLaunchKernel((const void*)k_zc_agree, dim3(1, 1, 1), dim3(64, 1, 1), args, 0, s));
+  g_launches.fetch_add(1);
+  return NBD_OK;
+}
+
 extern "C" {
 
 // ---- real ranks -----------------------------------------------------------
@@ -790,6 +956,29 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
                                  &prm);
     }
   }
+  if (auto_wanted(c, bytes)) {
+    // ordinary tensors: agree on the device whether every rank can address every rank's
+    // buffers; enqueue both kernels, the decision gates them (nbd_device.cuh)
+    const ExportRef es = export_ref(c, send, bytes, s);
+    const ExportRef er = (recv == send) ? es : export_ref(c, recv, bytes, s);
+    process_misses(c, s);
+    if ((rc = launch_agree(c, es, er, bytes, 1ull | ((u64)dtype << 8) | ((u64)op << 16), 3, send, recv, s)) != NBD_OK)
+      return rc;
+    PackZc<1> zk;
+    memset(&zk, 0, sizeof(zk));
+    zk.ctx[0] = c->ctx;
+    OpParams prm = zc_params(c, bytes, op, 0);
+    prm.zc_mode = 1;
+    if ((rc = launch_zc_reduce<1>(Z_AR, dtype, op, pick_blocks(c, ceil_div(ceil_div(bytes, kUnit), c->world), 0), 1, s,
+                                  zk, &prm)) != NBD_OK)
+      return rc;
+    Plan p = plan_all_reduce(c, bytes, op, 0);
+    p.op.zc_mode = 2;
+    Pack<1> pk;
+    fill_pack(pk, c, send, recv);
+    c->last_algo = "ar_auto";
+    return launch_reduce<1>(p.op.algo == 1 ? K_AR1 : K_AR2, dtype, op, p.nblocks, 1, s, pk, &p.op);
+  }
   Plan p = plan_all_reduce(c, bytes, op, 0);
   Pack<1> pk;
   fill_pack(pk, c, send, recv);
@@ -827,6 +1016,25 @@ int nbd_reduce_scatter(nbd_comm_t c, const void* send, void* recv, size_t recv_c
       c->last_algo = "reduce_scatter_zerocopy";
       return launch_zc_reduce<1>(Z_RS, dtype, op, pick_blocks(c, ceil_div(bytes, kUnit), 0), 1, s, zk, &prm);
     }
+  }
+  if (auto_wanted(c, bytes * c->world)) {
+    const ExportRef es = export_ref(c, send, bytes * c->world, s);
+    process_misses(c, s);
+    if ((rc = launch_agree(c, es, ExportRef(), bytes, 2ull | ((u64)dtype << 8) | ((u64)op << 16), 1, send, recv, s)) != NBD_OK)
+      return rc;
+    PackZc<1> zk;
+    memset(&zk, 0, sizeof(zk));
+    zk.ctx[0] = c->ctx;
+    OpParams prm = zc_params(c, bytes, op, 0);
+    prm.zc_mode = 1;
+    if ((rc = launch_zc_reduce<1>(Z_RS, dtype, op, pick_blocks(c, ceil_div(bytes, kUnit), 0), 1, s, zk, &prm)) != NBD_OK)
+      return rc;
+    Plan p = plan_reduce_scatter(c, bytes, op, 0);
+    p.op.zc_mode = 2;
+    Pack<1> pk;
+    fill_pack(pk, c, send, recv);
+    c->last_algo = "reduce_scatter_auto";
+    return launch_reduce<1>(K_RS, dtype, op, p.nblocks, 1, s, pk, &p.op);
   }
   Plan p = plan_reduce_scatter(c, bytes, op, 0);
   Pack<1> pk;
@@ -870,6 +1078,26 @@ int nbd_all_gather(nbd_comm_t c, const void* send, void* recv, size_t send_count
       c->last_algo = ks >= 0 ? "all_gather_zerocopy_pull" : "all_gather_zerocopy_push";
       return launch_ptr((const void*)k_all_gather_zc<1>, pick_blocks(c, ceil_div(bytes, kUnit), 0), 1, false, s, &zk, &prm);
     }
+  }
+  if (auto_wanted(c, bytes * c->world)) {
+    const ExportRef es = export_ref(c, send, bytes, s);  // pull: peers read our send buffer
+    process_misses(c, s);
+    int rc2 = launch_agree(c, es, ExportRef(), bytes, 3ull | (1ull << 8), 1, send, recv, s);
+    if (rc2 != NBD_OK) return rc2;
+    PackZc<1> zk;
+    memset(&zk, 0, sizeof(zk));
+    zk.ctx[0] = c->ctx;
+    OpParams prm = zc_params(c, bytes, 0, 0);
+    prm.zc_mode = 1;
+    if ((rc2 = launch_ptr((const void*)k_all_gather_zc<1>, pick_blocks(c, ceil_div(bytes, kUnit), 0), 1, false, s, &zk,
+                          &prm)) != NBD_OK)
+      return rc2;
+    Plan p = plan_all_gather(c, bytes, 0);
+    p.op.zc_mode = 2;
+    Pack<1> pk;
+    fill_pack(pk, c, send, recv);
+    c->last_algo = "all_gather_auto";
+    return launch_any<1>((const void*)k_all_gather<1>, p.nblocks, 1, s, pk, &p.op);
   }
   Plan p = plan_all_gather(c, bytes, 0);
   Pack<1> pk;
@@ -1263,4 +1491,15 @@ extern "C" int nbd_mem_free(nbd_comm_t c, void* ptr) {
     return NBD_OK;
   }
   return fail(NBD_ERR_INVALID_ARGUMENT, "pointer was not returned by nbd_mem_alloc on this communicator");
+}
+
+// 1 if the most recent auto-registered collective on `comm` ran zero-copy, 0 if it ran staged,
+// negative on error.  Synchronises the device (tests and diagnostics only).
+extern "C" int nbd_comm_last_zc_decision(nbd_comm_t c) {
+  if (!c) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  DeviceGuard g(c->device);
+  NBD_CUDA(cudaDeviceSynchronize());
+  unsigned int ok = 0;
+  NBD_CUDA(cudaMemcpy(&ok, &reinterpret_cast<LocalBlock*>(c->state)->dec.ok, sizeof(ok), cudaMemcpyDeviceToHost));
+  return (int)ok;
 }

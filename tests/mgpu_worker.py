@@ -158,6 +158,42 @@ def body(rank: int, world: int, port: int) -> None:
     torch.cuda.synchronize()
     del sym, sym2
 
+    # ---- auto-registration: ordinary tensors go zero-copy once every rank has imported them ---
+    numel = 5 << 20  # 20 MiB fp32 >= auto_min_bytes
+    t = torch.empty(numel + 64, dtype=torch.float32, device=dev)[32:32 + numel]  # offset view of an allocation
+    decisions = []
+    for it in range(4):
+        x = O.make_inputs(world, numel, "f32", seed=40 + it)
+        t.copy_(H.to_cuda(x[rank], "f32", dev))
+        dist.all_reduce(t)
+        assert be.last_algo() == "ar_auto", be.last_algo()
+        decisions.append(be.last_zc_decision())
+        H.assert_same(_np(t, "f32"), O.reduce_rank_order(x, "f32"), "f32", f"auto all_reduce iteration {it} (zc={decisions[-1]})")
+    # the first use of an allocation is staged (peers have not imported it yet) unless an earlier
+    # collective already touched the same caching-allocator segment; afterwards it is zero-copy
+    assert decisions[-1] == 1 and sorted(decisions) == decisions, decisions
+    allowed = _gather_cpu(dist, torch, torch.tensor(decisions))
+    assert all(torch.equal(a, allowed[0]) for a in allowed), "ranks took different paths"
+    shard = 3 << 20
+    xs = O.make_inputs(world, world * shard, "bf16", seed=50)
+    big_in = H.to_cuda(xs[rank], "bf16", dev)
+    o = torch.empty(shard, dtype=torch.bfloat16, device=dev)
+    full = torch.empty(world * shard, dtype=torch.bfloat16, device=dev)
+    rs_dec, ag_dec = [], []
+    for it in range(3):
+        dist.reduce_scatter_tensor(o, big_in)
+        rs_dec.append(be.last_zc_decision())
+        H.assert_same(_np(o, "bf16"), O.reduce_scatter(xs, "bf16")[rank], "bf16", f"auto reduce_scatter iteration {it}")
+        dist.all_gather_into_tensor(full, o)
+        ag_dec.append(be.last_zc_decision())
+        H.assert_same(_np(full, "bf16"), np.concatenate(O.reduce_scatter(xs, "bf16")), "bf16", f"auto all_gather iteration {it}")
+    assert rs_dec[-1] == 1 and ag_dec[-1] == 1, (rs_dec, ag_dec)
+    be.set_tunable("auto_register_off", 1)
+    dist.all_reduce(t)
+    assert be.last_algo() in ("ar_oneshot", "ar_twoshot")
+    be.set_tunable("auto_register_off", 0)
+    del t, big_in, o, full
+
     # ---- async ops, futures, barrier, non-contiguous rejection -----------------------------
     x = O.make_inputs(world, 1 << 20, "f32", seed=3)
     t = H.to_cuda(x[rank], "f32", dev)

@@ -425,6 +425,8 @@ def run_ours_multi(args):
     if not args.no_sweep:
         log("message-size sweep")
         extras["sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be)
+        log("device-side small-message latency")
+        extras["latency"] = kernel_latency(torch, dist, dev, world, cpu_group, be)
         log("registered-memory sweep")
         extras["registered"] = registered_sweep(torch, dist, dev, world, cpu_group, be)
     if not args.no_nccl:
@@ -496,6 +498,9 @@ def multi_sweep(torch, dist, dev, world, cpu_group, be):
     shard = torch.empty(flat.numel() // world, dtype=torch.bfloat16, device=dev)
     for name, fn in (("reduce_scatter", lambda: dist.reduce_scatter_tensor(shard, flat)),
                      ("all_gather", lambda: dist.all_gather_into_tensor(flat, shard))):
+        for _ in range(3):  # first touches export/import the allocations (auto-registration)
+            fn()
+            torch.cuda.synchronize()
         ms = _time_collective(torch, dist, fn, 5, 2, cpu_group)
         out.append({"op": name, "dtype": "bfloat16", "bytes": 1 << 30, "us": round(ms * 1e3, 2),
                     "busbw_per_rank": round((1 << 30) * (world - 1) / world / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
@@ -508,11 +513,37 @@ def multi_sweep(torch, dist, dev, world, cpu_group, be):
                 buf = torch.ones(nbytes // es, device=dev, dtype=dt)
                 iters = 100 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 5)
                 fn = (lambda: dist.all_reduce(buf)) if kind == "all_reduce" else (lambda: dist.broadcast(buf, src=0))
+                if nbytes >= (8 << 20):
+                    for _ in range(3):  # first touches export/import the allocation
+                        fn()
+                        torch.cuda.synchronize()
                 ms = _time_collective(torch, dist, fn, iters, 5 if nbytes <= (1 << 20) else 2, cpu_group)
                 factor = bus_factor(world) if kind == "all_reduce" else 1.0
                 out.append({"op": kind, "dtype": str(dt).replace("torch.", ""), "bytes": nbytes, "us": round(ms * 1e3, 2),
                             "busbw_per_rank": round(nbytes * factor / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
                 del buf
+    return out
+
+
+def kernel_latency(torch, dist, dev, world, cpu_group, be):
+    """Per-operation time of small all_reduces issued back to back from C++ (no Python between
+    launches): the device-side latency the 'single-digit-us' target is about."""
+    out = []
+    for nbytes in (8, 4 << 10, 64 << 10, 256 << 10, 1 << 20):
+        buf = torch.zeros(max(1, nbytes // 4), device=dev, dtype=torch.float32)
+        iters = 200
+        be.repeat_all_reduce(buf, 20)
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        be.repeat_all_reduce(buf, iters)
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
+        t = torch.tensor([e0.elapsed_time(e1) * 1e3 / iters], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
+        out.append({"op": "all_reduce", "bytes": nbytes, "us": round(float(t.item()), 2), "algo": be.last_algo()})
     return out
 
 

@@ -439,6 +439,25 @@ class BackendB200 : public c10d::Backend {
                          at::TensorOptions().dtype(dtype).device(c10::Device(c10::kCUDA, dev)));
   }
 
+  // Enqueue `iters` in-place SUM all_reduces of `t` back to back on the caller's stream without
+  // returning to Python in between: what bench.py times for the small-message latency, where
+  // the ~15 us of Python/c10d dispatch per dist.all_reduce call would otherwise hide the kernel.
+  void repeat_all_reduce(at::Tensor t, int64_t iters) {
+    check_tensor(t);
+    const int dtype = to_nbd_dtype(t.scalar_type(), true);
+    std::lock_guard<std::mutex> lk(mu_);
+    ensure_comm(t.get_device());
+    c10::cuda::CUDAGuard g(t.get_device());
+    auto stream = c10::cuda::getCurrentCUDAStream(t.get_device());
+    if (has_last_ && *last_stream_ != stream) last_done_.block(stream);
+    for (int64_t i = 0; i < iters; ++i)
+      NBD_CHECK(nbd_all_reduce(comm_, t.data_ptr(), t.data_ptr(), (size_t)t.numel(), dtype, NBD_SUM, stream.stream()),
+                "repeat_all_reduce");
+    last_done_.record(stream);
+    last_stream_ = stream;
+    has_last_ = true;
+  }
+
   // ---- extras exposed to Python ------------------------------------------------
   void set_tunable(const std::string& name, uint64_t value) {
     tunables_.emplace_back(name, value);
@@ -573,6 +592,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("set_tunable", &BackendB200::set_tunable)
       .def("last_algo", &BackendB200::last_algo)
       .def("last_zc_decision", &BackendB200::last_zc_decision)
+      .def("repeat_all_reduce", &BackendB200::repeat_all_reduce, py::call_guard<py::gil_scoped_release>())
       .def("device_index", &BackendB200::device_index)
       .def("set_inline_sync_ops", &BackendB200::set_inline_sync_ops);
   m.def("create_backend", &create_backend, py::arg("store"), py::arg("rank"), py::arg("size"), py::arg("timeout"),

@@ -78,6 +78,7 @@ struct nbd_comm {
   // tunables (0 = default)
   uint64_t t_blocks = 0, t_ar1_max = 0, t_bcast_direct_max = 0, t_chunk = 0;
   uint64_t t_zc_off = 0, t_zc_min = 0;  // zero-copy switch / size threshold
+  uint64_t t_zc_fused = 0, t_zc_tile = 0;  // all_reduce: 1 = fused loop, 2 = tiled; tile bytes (0 = whole span)
   struct Registration {                 // symmetric memory: same index on every rank
     char* base = nullptr;
     size_t bytes = 0;
@@ -386,6 +387,8 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "chunk_bytes")) return &c->t_chunk;
   if (!strcmp(name, "zero_copy_off")) return &c->t_zc_off;
   if (!strcmp(name, "zc_min_bytes")) return &c->t_zc_min;
+  if (!strcmp(name, "zc_ar_mode")) return &c->t_zc_fused;
+  if (!strcmp(name, "zc_tile_bytes")) return &c->t_zc_tile;
   if (!strcmp(name, "auto_register_off")) return &c->t_auto_off;
   if (!strcmp(name, "auto_min_bytes")) return &c->t_auto_min;
   return nullptr;
@@ -494,23 +497,31 @@ static int pick_blocks(const nbd_comm* c, u64 units_per_block_span, int emu_worl
 }
 
 // A message that fits one chunk gets a chunk of exactly its (aligned) size: CTA spans are
-// cut from chunk_bytes (see block_span), so an oversized chunk would idle most CTAs.
+// cut from chunk_bytes (see block_span), so an oversized chunk would idle most CTAs.  A larger
+// message is cut into EQUAL chunks: a short ragged last chunk leaves most CTAs idle for a whole
+// pipeline step (8xB200, 256 MiB: 3 chunks of 113+113+30 MiB 518 GB/s, 4 x 64 MiB 579 GB/s).
 static inline u64 fit_chunk(u64 chunk, u64 bytes, u64 align) {
-  if (bytes >= chunk) return chunk;
-  const u64 fit = ceil_div(bytes, align) * align;
-  return fit < chunk ? fit : chunk;
+  if (bytes == 0) return chunk;
+  const u64 n = ceil_div(bytes, chunk);
+  const u64 even = ceil_div(ceil_div(bytes, n), align) * align;
+  return even < chunk ? even : chunk;
 }
 
-static const u64 kDefChunkAR = 32ull << 20;    // message bytes per step
-static const u64 kDefChunkShard = 8ull << 20;  // shard bytes per step (rs / ag)
-static const u64 kDefChunkBcast = 32ull << 20;
+// Default pipeline chunk: 64 MiB of message (or what the staging half holds, if less).  Every
+// chunk costs one or two flag barriers: 8 MiB chunks measured 187 GB/s, 64 MiB 579 GB/s
+// (8xB200, 256 MiB; 2xB200: 387 vs 555; profiles/r01_tune_n{2,8}.jsonl).  "chunk_bytes" overrides.
+static const u64 kDefChunkAR = 64ull << 20;
+static const u64 kDefChunkShard = 64ull << 20;
+static const u64 kDefChunkBcast = 64ull << 20;
 
 static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
   Plan p;
   memset(&p, 0, sizeof(p));
   const int N = c->world;
   const u64 half = c->ctx.half_bytes;
-  const u64 ar1_max = c->t_ar1_max ? c->t_ar1_max : (N == 2 ? ~0ull : (512ull << 10));
+  // one-shot moves N/2 times the bytes of two-shot but has one barrier: 8xB200 1 MiB 31 us vs 54 us,
+  // 4 MiB 64 us vs 59 us (profiles/r01_tune_n8.jsonl); with two ranks it moves the same bytes
+  const u64 ar1_max = c->t_ar1_max ? c->t_ar1_max : (N == 2 ? ~0ull : (2ull << 20));
   p.op.bytes = bytes;
   p.op.op = op;
   p.op.avg = (op == NBD_AVG);
@@ -518,7 +529,7 @@ static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
   if (bytes <= ar1_max) {
     p.op.algo = 1;
     u64 cap = floor_to(half / N, kUnit);
-    u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkAR / N;
+    u64 chunk = c->t_chunk ? floor_to(c->t_chunk, kUnit) : kDefChunkAR;
     if (chunk < kUnit) chunk = kUnit;
     if (chunk > cap) chunk = cap;
     chunk = fit_chunk(chunk, bytes, kUnit);
@@ -708,10 +719,13 @@ static int fill_pack_emu(Pack<kMaxRanks>& pk, EmuGroup* g, const void* const* se
 // ---------------------------------------------------------------------------
 // zero-copy: registration lookup, planning, launch
 // ---------------------------------------------------------------------------
-static const u64 kDefZcMin = 256ull << 10;
+// Registered buffers: below ~32 MiB the staged kernels are as fast or faster (2xB200: 16 MiB staged
+// 40 us vs zero-copy 46 us, 64 MiB 143 vs 123; 8xB200: 16 MiB 89 vs 96, 64 MiB 234 vs 222).
+static const u64 kDefZcMin = 32ull << 20;
 
 static bool zc_wanted(const nbd_comm* c, u64 bytes) {
-  return !c->t_zc_off && bytes >= (c->t_zc_min ? c->t_zc_min : kDefZcMin);
+  // emulated ranks have no NVLink round trips to amortise: zero-copy halves the HBM traffic at any size
+  return !c->t_zc_off && bytes >= (c->t_zc_min ? c->t_zc_min : (c->emu ? (256ull << 10) : kDefZcMin));
 }
 
 // index of the connected registration that contains [ptr, ptr+bytes), or -1
@@ -767,6 +781,13 @@ static OpParams zc_params(const nbd_comm* c, u64 bytes, int op, int algo) {
   return p;
 }
 
+// all_reduce zero-copy variant: fused loop for two ranks, tiled read-then-push beyond
+static void zc_ar_variant(const nbd_comm* c, OpParams* p) {
+  const bool tiled = c->t_zc_fused ? (c->t_zc_fused == 2) : (c->world > 2);
+  p->algo = tiled ? 1 : 0;
+  p->chunk_bytes = tiled ? c->t_zc_tile : 0;
+}
+
 static int fill_zc_emu(PackZc<kMaxRanks>& pk, EmuGroup* g, const void* const* sends, void* const* recvs) {
   memset(&pk, 0, sizeof(pk));
   for (int r = 0; r < g->world; ++r) {
@@ -789,7 +810,9 @@ static void set_algo(nbd_comm* c, const char* name) {
 // ---------------------------------------------------------------------------
 // auto-registration of ordinary (unregistered) buffers — see nbd_device.cuh
 // ---------------------------------------------------------------------------
-static const u64 kDefAutoMin = 8ull << 20;
+// Below this the agreement kernel (~15 us) costs more than zero-copy saves (2xB200: 16 MiB staged
+// 40 us vs auto 62 us; 64 MiB 143 vs 139; 256 MiB 498 vs 444; profiles/r01_tune_n2.jsonl).
+static const u64 kDefAutoMin = 64ull << 20;
 
 typedef CUresult (*PFN_cuPointerGetAttribute)(void*, CUpointer_attribute, CUdeviceptr);
 typedef CUresult (*PFN_cuMemGetAddressRange)(CUdeviceptr*, size_t*, CUdeviceptr);
@@ -813,6 +836,12 @@ static void load_driver_entry_points() {
 static bool auto_wanted(const nbd_comm* c, u64 bytes) {
   return !c->emu && c->world > 1 && !c->t_zc_off && !c->t_auto_off &&
          bytes >= (c->t_auto_min ? c->t_auto_min : kDefAutoMin);
+}
+
+// all_reduce: with more than two ranks the staged two-shot is already within 3 % of zero-copy
+// (8xB200, 256 MiB: 579 vs 578 GB/s), so the agreement only pays for itself on larger messages
+static bool auto_wanted_ar(const nbd_comm* c, u64 bytes) {
+  return auto_wanted(c, bytes) && (c->t_auto_min || c->world <= 2 || bytes >= (512ull << 20));
 }
 
 struct ExportRef {
@@ -951,12 +980,13 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
       const u64 d[6] = {(u64)ks, offs, (u64)kr, offr, bytes, 1ull | ((u64)dtype << 8) | ((u64)op << 16)};
       memcpy(zk.z.desc, d, sizeof(d));
       OpParams prm = zc_params(c, bytes, op, 0);
+      zc_ar_variant(c, &prm);
       c->last_algo = "ar_zerocopy";
       return launch_zc_reduce<1>(Z_AR, dtype, op, pick_blocks(c, ceil_div(ceil_div(bytes, kUnit), c->world), 0), 1, s, zk,
                                  &prm);
     }
   }
-  if (auto_wanted(c, bytes)) {
+  if (auto_wanted_ar(c, bytes)) {
     // ordinary tensors: agree on the device whether every rank can address every rank's
     // buffers; enqueue both kernels, the decision gates them (nbd_device.cuh)
     const ExportRef es = export_ref(c, send, bytes, s);
@@ -968,6 +998,7 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
     memset(&zk, 0, sizeof(zk));
     zk.ctx[0] = c->ctx;
     OpParams prm = zc_params(c, bytes, op, 0);
+    zc_ar_variant(c, &prm);
     prm.zc_mode = 1;
     if ((rc = launch_zc_reduce<1>(Z_AR, dtype, op, pick_blocks(c, ceil_div(ceil_div(bytes, kUnit), c->world), 0), 1, s,
                                   zk, &prm)) != NBD_OK)
@@ -1175,6 +1206,7 @@ int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* re
     PackZc<kMaxRanks> zk;
     if ((rc = fill_zc_emu(zk, g, sends, recvs)) != NBD_OK) return rc;
     OpParams prm = zc_params(c0, bytes, op, 0);
+    zc_ar_variant(c0, &prm);
     set_algo(c0, "ar_zerocopy");
     return launch_zc_reduce<kMaxRanks>(Z_AR, dtype, op, pick_blocks(c0, ceil_div(ceil_div(bytes, kUnit), g->world), g->world),
                                        g->world, s, zk, &prm);

@@ -116,6 +116,7 @@ def body(rank: int, world: int, port: int) -> None:
 
     # ---- symmetric memory (Backend.allocate_tensor): zero-copy kernels over NVLink ----------
     assert be.supports_tensor_alloc(dev)
+    be.set_tunable("zc_min_bytes", 256 << 10)  # default is 4 MiB; exercise the zero-copy kernels on smaller messages too
     n_sym = (6 << 20) + 64
     sym = B.empty_symmetric(n_sym, torch.float32)
     sym2 = B.empty_symmetric(n_sym, torch.bfloat16)
@@ -156,10 +157,12 @@ def body(rank: int, world: int, port: int) -> None:
     dist.all_reduce(sym[:shard])
     dist.all_reduce(y)
     torch.cuda.synchronize()
+    be.set_tunable("zc_min_bytes", 0)
     del sym, sym2
 
     # ---- auto-registration: ordinary tensors go zero-copy once every rank has imported them ---
-    numel = 5 << 20  # 20 MiB fp32 >= auto_min_bytes
+    be.set_tunable("auto_min_bytes", 1 << 20)  # default is 64 MiB
+    numel = 5 << 20  # 20 MiB fp32
     t = torch.empty(numel + 64, dtype=torch.float32, device=dev)[32:32 + numel]  # offset view of an allocation
     decisions = []
     for it in range(4):
@@ -192,6 +195,7 @@ def body(rank: int, world: int, port: int) -> None:
     dist.all_reduce(t)
     assert be.last_algo() in ("ar_oneshot", "ar_twoshot")
     be.set_tunable("auto_register_off", 0)
+    be.set_tunable("auto_min_bytes", 0)
     del t, big_in, o, full
 
     # ---- async ops, futures, barrier, non-contiguous rejection -----------------------------

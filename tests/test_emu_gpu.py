@@ -434,3 +434,20 @@ def test_invalid_arguments_are_rejected(torch_cuda, groups):
     empty = [torch.zeros(0, device="cuda:0") for _ in range(2)]
     grp.all_reduce(empty, empty)  # empty tensors are a no-op, not an error
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("mode,tile", [(1, 0), (2, 0), (2, 64 << 10), (2, 8192)])
+def test_zero_copy_all_reduce_variants(torch_cuda, groups, world, mode, tile):
+    """Fused and tiled (read-then-push) zero-copy all_reduce, in place and out of place."""
+    with tuned(groups(world), zc_min_bytes=1, zc_ar_mode=mode, zc_tile_bytes=tile) as grp:
+        for dtype, numel in (("f32", (1 << 20) + 7), ("bf16", 300001)):
+            x = O.make_inputs(world, numel, dtype)
+            want = O.all_reduce(x, dtype, "sum")
+            for inplace in (True, False):
+                got, sends = _run_all_reduce(torch_cuda, grp, x, dtype, inplace=inplace)
+                assert grp.last_algo() == "ar_zerocopy"
+                for r in range(world):
+                    H.assert_same(got[r], want[r], dtype, f"mode {mode} tile {tile} rank {r} inplace={inplace}")
+                    if not inplace:
+                        H.assert_same(sends[r], x[r], dtype, "send buffer modified")

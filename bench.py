@@ -266,7 +266,9 @@ def run_ours_single(args):
     peak, peak_src = measured_hbm_peak()
     alg_bytes = 2.0 * R * S  # every rank's input read once + every rank's output written once
     achieved = alg_bytes / (ms * 1e-3) / 1e9
-    traffic = recorded_traffic(f"emu{R}_allreduce_f32_{S >> 20}MiB")
+    traffic = recorded_traffic(f"emu{R}_{algo}_f32_{S >> 20}MiB")
+    kernel = {"ar_zerocopy": "nbd::k_allreduce_zc<float,true,8>", "ar_twoshot": "nbd::k_allreduce_twoshot<float,true,8>",
+              "ar_oneshot": "nbd::k_allreduce_oneshot<float,true,8>"}.get(algo, algo)
 
     extras = {}
     if not args.no_sweep:
@@ -290,8 +292,8 @@ def run_ours_single(args):
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes,
-                     "kernel": "nbd::k_allreduce_twoshot<float,true,8>",
-                     "note": "algorithmic bytes = minimal 2*R*S; the staged algorithm itself moves (5R-2)*S"},
+                     "kernel": kernel,
+                     "note": "algorithmic bytes = 2*R*S: every rank's input read once, every rank's output written once"},
     }
     line.update(extras)
     if not args.no_cpu_baseline:

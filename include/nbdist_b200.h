@@ -202,6 +202,19 @@ int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends,
                            int op, void* stream);
 int nbd_emu_barrier(nbd_comm_t any, void* stream);
 
+/* ---- host buffers -------------------------------------------------------------
+ * all_reduce of data that lives in HOST memory (pinned memory recommended): the call a host
+ * makes when its tensors are on the CPU side, e.g. the reference's gloo users
+ * (ref:src/nbdistributed/worker.py:146-147) moving to GPUs without changing where their data
+ * lives.  The library pipelines H2D copy, collective and D2H copy in "host_chunk_bytes"
+ * (tunable, default 32 MiB) chunks over three internal streams and a ring of device bounce
+ * buffers (allocated on first use), so PCIe runs in both directions at once.  Ordered after
+ * prior work on `stream`; `stream` waits for the result.  host_send may equal host_recv. */
+int nbd_all_reduce_host(nbd_comm_t comm, const void* host_send, void* host_recv, size_t count,
+                        int dtype, int op, void* stream);
+int nbd_emu_all_reduce_host(nbd_comm_t any, const void* const* host_sends, void* const* host_recvs,
+                            size_t count, int dtype, int op, void* stream);
+
 /* ---- allocation-free variant ------------------------------------------------
  * No counterpart in the reference.
  * The all-reduce of nbd_emu_all_reduce (world_size buffers that all live on the CURRENT

@@ -75,6 +75,17 @@ def empty_symmetric(numel: int, dtype=None, group=None):
     return be.allocate_tensor(int(numel), dtype=dtype or torch.float32, device=torch.device("cuda", torch.cuda.current_device()))
 
 
+def all_reduce_host(tensor, out=None, op: int = 0, group=None):
+    """all_reduce of a CPU tensor (pinned memory recommended) through the GPUs of ``group``.
+
+    The data stays host-resident for the caller: the library streams it through the GPU in
+    chunks, overlapping the H2D copy, the NVLink collective and the D2H copy.  ``op`` is the
+    c10d ReduceOp number (0 = SUM).  In place unless ``out`` is given.  Blocks until done."""
+    be = get_backend(group)
+    be.all_reduce_host(tensor, tensor if out is None else out, int(op))
+    return tensor if out is None else out
+
+
 def launch_count() -> int:
     """Kernels launched by the native library in this process (bench.py's gpu_launches)."""
     return int(_load_ext().launch_count())

@@ -35,6 +35,7 @@ SYMBOLS = [
     "nbd_emu_create", "nbd_emu_destroy",
     "nbd_all_reduce", "nbd_broadcast", "nbd_all_gather", "nbd_reduce_scatter", "nbd_barrier",
     "nbd_emu_all_reduce", "nbd_emu_broadcast", "nbd_emu_all_gather", "nbd_emu_reduce_scatter", "nbd_emu_barrier",
+    "nbd_all_reduce_host", "nbd_emu_all_reduce_host",
     "nbd_local_all_reduce_noalloc",
     "nbd_comm_last_zc_decision",
     "nbd_launch_count", "nbd_last_algo",
@@ -94,6 +95,8 @@ def load() -> C.CDLL:
         "nbd_emu_all_gather": (i, [vp, pp, pp, sz, i, vp]),
         "nbd_emu_reduce_scatter": (i, [vp, pp, pp, sz, i, i, vp]),
         "nbd_emu_barrier": (i, [vp, vp]),
+        "nbd_all_reduce_host": (i, [vp, vp, vp, sz, i, i, vp]),
+        "nbd_emu_all_reduce_host": (i, [vp, pp, pp, sz, i, i, vp]),
         "nbd_local_all_reduce_noalloc": (i, [pp, pp, i, sz, i, i, vp]),
         "nbd_comm_last_zc_decision": (i, [vp]),
         "nbd_launch_count": (u64, []),
@@ -195,6 +198,14 @@ class EmuGroup:
         t = sends[0]
         check(self.lib.nbd_emu_all_reduce(self._h, _ptr_array(sends), _ptr_array(recvs), t.numel(),
                                           torch_dtype_code(t.dtype), op, _stream_handle(stream)))
+
+    def all_reduce_host(self, host_sends, host_recvs=None, op: int = SUM, stream=None) -> None:
+        """all_reduce of (pinned) CPU tensors: chunked H2D / collective / D2H pipeline in the library."""
+        host_recvs = host_sends if host_recvs is None else host_recvs
+        t = host_sends[0]
+        assert not t.is_cuda, "all_reduce_host takes CPU tensors"
+        check(self.lib.nbd_emu_all_reduce_host(self._h, _ptr_array(host_sends), _ptr_array(host_recvs), t.numel(),
+                                               torch_dtype_code(t.dtype), op, _stream_handle(stream)))
 
     def broadcast(self, bufs, root: int = 0, stream=None) -> None:
         t = bufs[0]

@@ -458,6 +458,31 @@ class BackendB200 : public c10d::Backend {
     has_last_ = true;
   }
 
+  // all_reduce of CPU tensors through the GPUs: nbd_all_reduce_host pipelines H2D, the
+  // collective and D2H in chunks.  Returns when `recv` holds the result (CPU-tensor semantics).
+  void all_reduce_host(at::Tensor send, at::Tensor recv, int64_t op) {
+    TORCH_CHECK(send.device().is_cpu() && recv.device().is_cpu(), "[b200] all_reduce_host takes CPU tensors");
+    TORCH_CHECK(send.is_contiguous() && recv.is_contiguous(), "Tensors must be contiguous");
+    TORCH_CHECK(send.scalar_type() == recv.scalar_type() && send.numel() == recv.numel(),
+                "[b200] all_reduce_host: send and recv must match");
+    const int dtype = to_nbd_dtype(send.scalar_type(), true);
+    std::lock_guard<std::mutex> lk(mu_);
+    const c10::DeviceIndex dev = comm_ ? device_ : c10::cuda::current_device();
+    ensure_comm(dev);
+    c10::cuda::CUDAGuard g(dev);
+    auto stream = c10::cuda::getCurrentCUDAStream(dev);
+    if (has_last_ && *last_stream_ != stream) last_done_.block(stream);
+    NBD_CHECK(nbd_all_reduce_host(comm_, send.data_ptr(), recv.data_ptr(), (size_t)send.numel(), dtype, (int)op,
+                                  stream.stream()),
+              "all_reduce_host");
+    last_done_.record(stream);
+    last_stream_ = stream;
+    has_last_ = true;
+    C10_CUDA_CHECK(cudaStreamSynchronize(stream));
+    int rc = nbd_comm_async_error(comm_);
+    if (rc != NBD_OK) throw_nbd(rc, "all_reduce_host");
+  }
+
   // ---- extras exposed to Python ------------------------------------------------
   void set_tunable(const std::string& name, uint64_t value) {
     tunables_.emplace_back(name, value);
@@ -592,6 +617,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("set_tunable", &BackendB200::set_tunable)
       .def("last_algo", &BackendB200::last_algo)
       .def("last_zc_decision", &BackendB200::last_zc_decision)
+      .def("all_reduce_host", &BackendB200::all_reduce_host, py::arg("send"), py::arg("recv"), py::arg("op") = 0,
+           py::call_guard<py::gil_scoped_release>())
       .def("repeat_all_reduce", &BackendB200::repeat_all_reduce, py::call_guard<py::gil_scoped_release>())
       .def("device_index", &BackendB200::device_index)
       .def("set_inline_sync_ops", &BackendB200::set_inline_sync_ops);

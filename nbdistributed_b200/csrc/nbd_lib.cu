@@ -63,6 +63,20 @@ struct DeviceGuard {
 // ---------------------------------------------------------------------------
 struct EmuGroup;
 
+// Host-buffer collectives (nbd_*_host): three streams and a ring of device bounce buffers so
+// that the H2D copy of chunk k+1, the collective on chunk k and the D2H copy of chunk k-1
+// overlap; PCIe is full duplex, so a step costs ~max(H2D, D2H) instead of their sum.
+constexpr int kPipeSlots = 3;
+struct HostPipe {
+  bool ready = false;
+  int nranks = 0;        // 1 for a real rank, R for an emulated group
+  size_t chunk = 0;      // bytes per bounce buffer
+  cudaStream_t h2d = nullptr, comp = nullptr, d2h = nullptr;
+  cudaEvent_t ev_start = nullptr, ev_h2d[kPipeSlots] = {}, ev_comp[kPipeSlots] = {}, ev_d2h[kPipeSlots] = {};
+  bool used[kPipeSlots] = {};
+  char* buf[kMaxRanks][kPipeSlots] = {};
+};
+
 struct nbd_comm {
   int rank = 0, world = 1, device = 0;
   int num_sms = 0;
@@ -99,6 +113,8 @@ struct nbd_comm {
   ExportSlot* import_tmp = nullptr;             // pinned scratch for one slot
   uint64_t* imp_tmp = nullptr;                  // pinned ring of pointers handed to cudaMemcpyAsync
   int imp_tmp_n = 0;
+  uint64_t t_host_chunk = 0;
+  HostPipe hp;
   uint64_t timeout_ms = 600000;
   const char* last_algo = "none";
 };
@@ -106,6 +122,7 @@ struct nbd_comm {
 struct EmuGroup {
   int world = 0;
   nbd_comm* comms[kMaxRanks] = {};
+  HostPipe hp;
 };
 
 struct Handle {  // serialised into NBD_HANDLE_BYTES
@@ -197,12 +214,30 @@ static void fill_ctx(nbd_comm* c) {
   x.timeout_ns = c->timeout_ms * 1000000ull;
 }
 
+static void hostpipe_free(HostPipe& hp) {
+  if (!hp.ready) return;
+  for (int r = 0; r < kMaxRanks; ++r)
+    for (int k = 0; k < kPipeSlots; ++k)
+      if (hp.buf[r][k]) cudaFree(hp.buf[r][k]);
+  for (int k = 0; k < kPipeSlots; ++k) {
+    cudaEventDestroy(hp.ev_h2d[k]);
+    cudaEventDestroy(hp.ev_comp[k]);
+    cudaEventDestroy(hp.ev_d2h[k]);
+  }
+  cudaEventDestroy(hp.ev_start);
+  cudaStreamDestroy(hp.h2d);
+  cudaStreamDestroy(hp.comp);
+  cudaStreamDestroy(hp.d2h);
+  hp = HostPipe();
+}
+
 static void free_rank(nbd_comm* c) {
   if (c->mbox) c->mbox->abort = 1;  // let any stuck flag wait leave before cudaFree's implicit sync
   if (!c->emu) {
     for (int p = 0; p < c->world; ++p)
       if (p != c->rank && c->peer_base[p]) cudaIpcCloseMemHandle(c->peer_base[p]);
   }
+  hostpipe_free(c->hp);
   for (auto& g : c->regs) {
     if (!c->emu)
       for (int p = 0; p < c->world; ++p)
@@ -389,6 +424,7 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "zc_min_bytes")) return &c->t_zc_min;
   if (!strcmp(name, "zc_ar_mode")) return &c->t_zc_fused;
   if (!strcmp(name, "zc_tile_bytes")) return &c->t_zc_tile;
+  if (!strcmp(name, "host_chunk_bytes")) return &c->t_host_chunk;
   if (!strcmp(name, "auto_register_off")) return &c->t_auto_off;
   if (!strcmp(name, "auto_min_bytes")) return &c->t_auto_min;
   return nullptr;
@@ -461,6 +497,7 @@ int nbd_emu_destroy(nbd_comm_t any) {
   if (!any->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "not an emulated communicator");
   EmuGroup* grp = any->group;
   DeviceGuard g(any->device);
+  hostpipe_free(grp->hp);
   for (int r = 0; r < grp->world; ++r) {
     free_rank(grp->comms[r]);
     delete grp->comms[r];
@@ -1534,4 +1571,107 @@ extern "C" int nbd_comm_last_zc_decision(nbd_comm_t c) {
   unsigned int ok = 0;
   NBD_CUDA(cudaMemcpy(&ok, &reinterpret_cast<LocalBlock*>(c->state)->dec.ok, sizeof(ok), cudaMemcpyDeviceToHost));
   return (int)ok;
+}
+
+// ---------------------------------------------------------------------------
+// host-buffer all_reduce (see include/nbdist_b200.h): chunked H2D -> collective -> D2H pipeline
+// ---------------------------------------------------------------------------
+static const size_t kDefHostChunk = 32ull << 20;
+
+static int hostpipe_init(HostPipe& hp, int nranks, size_t chunk) {
+  if (hp.ready && hp.nranks == nranks && hp.chunk == chunk) return NBD_OK;
+  hostpipe_free(hp);
+  hp.nranks = nranks;
+  hp.chunk = chunk;
+  NBD_CUDA(cudaStreamCreateWithFlags(&hp.h2d, cudaStreamNonBlocking));
+  NBD_CUDA(cudaStreamCreateWithFlags(&hp.comp, cudaStreamNonBlocking));
+  NBD_CUDA(cudaStreamCreateWithFlags(&hp.d2h, cudaStreamNonBlocking));
+  NBD_CUDA(cudaEventCreateWithFlags(&hp.ev_start, cudaEventDisableTiming));
+  for (int k = 0; k < kPipeSlots; ++k) {
+    NBD_CUDA(cudaEventCreateWithFlags(&hp.ev_h2d[k], cudaEventDisableTiming));
+    NBD_CUDA(cudaEventCreateWithFlags(&hp.ev_comp[k], cudaEventDisableTiming));
+    NBD_CUDA(cudaEventCreateWithFlags(&hp.ev_d2h[k], cudaEventDisableTiming));
+    for (int r = 0; r < nranks; ++r) NBD_CUDA(cudaMalloc((void**)&hp.buf[r][k], chunk));
+  }
+  hp.ready = true;
+  return NBD_OK;
+}
+
+// One pipelined pass.  `reduce(slot, bytes, stream)` enqueues the collective on the bounce
+// buffers of `slot`.
+template <typename F>
+static int hostpipe_run(HostPipe& hp, const void* const* hsend, void* const* hrecv, u64 bytes, cudaStream_t user, F reduce) {
+  NBD_CUDA(cudaEventRecord(hp.ev_start, user));
+  NBD_CUDA(cudaStreamWaitEvent(hp.h2d, hp.ev_start, 0));
+  NBD_CUDA(cudaStreamWaitEvent(hp.comp, hp.ev_start, 0));
+  const u64 nchunks = ceil_div(bytes, (u64)hp.chunk);
+  int last_slot = 0;
+  for (u64 k = 0; k < nchunks; ++k) {
+    const int slot = (int)(k % kPipeSlots);
+    const u64 off = k * hp.chunk;
+    const u64 n = bytes - off < hp.chunk ? bytes - off : hp.chunk;
+    if (hp.used[slot]) NBD_CUDA(cudaStreamWaitEvent(hp.h2d, hp.ev_d2h[slot], 0));  // bounce buffer drained
+    for (int r = 0; r < hp.nranks; ++r)
+      NBD_CUDA(cudaMemcpyAsync(hp.buf[r][slot], (const char*)hsend[r] + off, n, cudaMemcpyHostToDevice, hp.h2d));
+    NBD_CUDA(cudaEventRecord(hp.ev_h2d[slot], hp.h2d));
+    NBD_CUDA(cudaStreamWaitEvent(hp.comp, hp.ev_h2d[slot], 0));
+    int rc = reduce(slot, n, hp.comp);
+    if (rc != NBD_OK) return rc;
+    NBD_CUDA(cudaEventRecord(hp.ev_comp[slot], hp.comp));
+    NBD_CUDA(cudaStreamWaitEvent(hp.d2h, hp.ev_comp[slot], 0));
+    for (int r = 0; r < hp.nranks; ++r)
+      NBD_CUDA(cudaMemcpyAsync((char*)hrecv[r] + off, hp.buf[r][slot], n, cudaMemcpyDeviceToHost, hp.d2h));
+    NBD_CUDA(cudaEventRecord(hp.ev_d2h[slot], hp.d2h));
+    hp.used[slot] = true;
+    last_slot = slot;
+  }
+  NBD_CUDA(cudaStreamWaitEvent(user, hp.ev_d2h[last_slot], 0));  // d2h is in order: all chunks are back
+  return NBD_OK;
+}
+
+static size_t host_chunk_bytes(const nbd_comm* c) {
+  size_t chunk = c->t_host_chunk ? (size_t)c->t_host_chunk : kDefHostChunk;
+  chunk = (chunk + 255) / 256 * 256;
+  return chunk;
+}
+
+extern "C" int nbd_all_reduce_host(nbd_comm_t c, const void* host_send, void* host_recv, size_t count, int dtype, int op,
+                                   void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_all_reduce_host with emulated communicators");
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (count == 0) return NBD_OK;
+  if (!host_send || !host_recv) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer");
+  DeviceGuard g(c->device);
+  const size_t es = nbd_dtype_size(dtype);
+  if ((rc = hostpipe_init(c->hp, 1, host_chunk_bytes(c))) != NBD_OK) return rc;
+  const void* hs[1] = {host_send};
+  void* hr[1] = {host_recv};
+  HostPipe& hp = c->hp;
+  return hostpipe_run(hp, hs, hr, (u64)count * es, (cudaStream_t)stream, [&](int slot, u64 n, cudaStream_t s) {
+    return nbd_all_reduce(c, hp.buf[0][slot], hp.buf[0][slot], (size_t)(n / es), dtype, op, s);
+  });
+}
+
+extern "C" int nbd_emu_all_reduce_host(nbd_comm_t any, const void* const* host_sends, void* const* host_recvs, size_t count,
+                                       int dtype, int op, void* stream) {
+  int rc;
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (any && any->emu && count == 0) return NBD_OK;
+  if ((rc = emu_check(any, host_sends, (const void* const*)host_recvs, true)) != NBD_OK) return rc;
+  EmuGroup* g = any->group;
+  DeviceGuard dg(g->comms[0]->device);
+  const size_t es = nbd_dtype_size(dtype);
+  if ((rc = hostpipe_init(g->hp, g->world, host_chunk_bytes(g->comms[0]))) != NBD_OK) return rc;
+  HostPipe& hp = g->hp;
+  return hostpipe_run(hp, host_sends, host_recvs, (u64)count * es, (cudaStream_t)stream, [&](int slot, u64 n, cudaStream_t s) {
+    const void* sends[kMaxRanks];
+    void* recvs[kMaxRanks];
+    for (int r = 0; r < g->world; ++r) {
+      sends[r] = hp.buf[r][slot];
+      recvs[r] = hp.buf[r][slot];
+    }
+    return nbd_emu_all_reduce(any, sends, recvs, (size_t)(n / es), dtype, op, s);
+  });
 }

@@ -198,6 +198,20 @@ def body(rank: int, world: int, port: int) -> None:
     be.set_tunable("auto_min_bytes", 0)
     del t, big_in, o, full
 
+    # ---- host buffers: CPU tensors all-reduced through the GPUs, vs gloo on the same tensors ----
+    be.set_tunable("host_chunk_bytes", 4 << 20)
+    xh = O.make_inputs(world, (5 << 20) + 3, "i32", seed=60)
+    h_in = torch.from_numpy(xh[rank].copy()).pin_memory()
+    h_out = torch.zeros_like(h_in).pin_memory()
+    B.all_reduce_host(h_in, out=h_out)
+    ref = h_in.clone()
+    dist.all_reduce(ref)  # CPU tensor -> gloo
+    assert torch.equal(h_out, ref), "all_reduce_host differs from gloo (int32, bit-exact)"
+    hf = torch.from_numpy(O.make_inputs(world, 300001, "f32", seed=61)[rank].copy()).pin_memory()
+    B.all_reduce_host(hf)
+    H.assert_same(hf.numpy(), O.reduce_rank_order(O.make_inputs(world, 300001, "f32", seed=61), "f32"), "f32", "all_reduce_host f32")
+    be.set_tunable("host_chunk_bytes", 0)
+
     # ---- async ops, futures, barrier, non-contiguous rejection -----------------------------
     x = O.make_inputs(world, 1 << 20, "f32", seed=3)
     t = H.to_cuda(x[rank], "f32", dev)

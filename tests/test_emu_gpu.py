@@ -451,3 +451,31 @@ def test_zero_copy_all_reduce_variants(torch_cuda, groups, world, mode, tile):
                     H.assert_same(got[r], want[r], dtype, f"mode {mode} tile {tile} rank {r} inplace={inplace}")
                     if not inplace:
                         H.assert_same(sends[r], x[r], dtype, "send buffer modified")
+
+
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("dtype,numel,chunk", [("f32", (3 << 20) + 5, 1 << 20), ("bf16", 100001, 64 << 10), ("i32", 777, 0)])
+def test_all_reduce_host_buffers(torch_cuda, groups, world, dtype, numel, chunk):
+    """nbd_emu_all_reduce_host: pinned host tensors in, pinned host tensors out, pipelined in chunks
+    (several chunks, ragged last one, more chunks than bounce buffers)."""
+    torch = torch_cuda
+    with tuned(groups(world), host_chunk_bytes=chunk) as grp:
+        x = O.make_inputs(world, numel, dtype)
+        tdt = H.torch_dtype(dtype)
+        hin = []
+        for a in x:
+            t = torch.empty(numel, dtype=tdt).pin_memory()
+            t.copy_(H.to_cuda(a, dtype).cpu())
+            hin.append(t)
+        hout = [torch.zeros(numel, dtype=tdt).pin_memory() for _ in range(world)]
+        for _ in range(2):  # twice: the bounce-buffer ring is reused across calls
+            grp.all_reduce_host(hin, hout)
+        torch.cuda.synchronize()
+        grp.async_error()
+        want = O.reduce_rank_order(x, dtype)
+        for r in range(world):
+            H.assert_same(H.to_numpy(hout[r], dtype), want, dtype, f"rank {r}")
+            H.assert_same(H.to_numpy(hin[r], dtype), x[r], dtype, f"host input of rank {r} modified")
+        grp.all_reduce_host(hin)  # in place
+        torch.cuda.synchronize()
+        H.assert_same(H.to_numpy(hin[0], dtype), want, dtype, "in place")

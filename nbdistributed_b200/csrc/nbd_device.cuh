@@ -36,6 +36,7 @@ struct LocalState {
   u64 chunk_seq;  // staging steps consumed; parity picks the staging half
   u32 done;       // CTAs of the running launch that have finished
   u32 pad;
+  u64 ll_seq;     // LL (flag-in-data) operations completed; parity picks the LL buffer
 };
 
 // Pinned host memory, visible to the device: async error reporting + abort.
@@ -57,7 +58,14 @@ struct RankCtx {
   HostMailbox* mbox;
   u64 half_bytes;   // bytes in one staging half (multiple of 16)
   u64 timeout_ns;   // 0 = never
+  u64 ll_off;       // offset of the LL area inside every rank's staging (0: no LL area)
 };
+
+// LL ("low latency") area at the tail of the staging region: for each parity, one slot per
+// source rank; a slot holds kLLMaxBytes of payload as 8-byte {data32, flag32} packets.
+constexpr u64 kLLMaxBytes = 32ull << 10;
+constexpr u64 kLLSlotBytes = 2 * kLLMaxBytes;
+constexpr u64 kLLAreaBytes = 2 * (u64)kMaxRanks * kLLSlotBytes;  // 1 MiB
 
 struct RankBufs {
   const char* send;

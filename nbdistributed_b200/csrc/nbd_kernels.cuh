@@ -175,6 +175,99 @@ k_allreduce_oneshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   kernel_end(c, op.nchunks, op.nchunks);
 }
 
+
+// ---------------------------------------------------------------------------
+// all_reduce, LL one-shot (latency path, <= kLLMaxBytes): every 4-byte word travels with its
+// own 4-byte flag in one 8-byte packet, so the receiver needs no separate flag, no fence and
+// no barrier: it spins on the packets themselves.  A unit of 16 payload bytes is two 16-byte
+// stores {w0,f,w1,f} {w2,f,w3,f}; each 8-byte half is written atomically.  flag = operation
+// sequence number (never 0), buffers alternate by its parity: a rank can run at most one LL
+// operation ahead of a peer (it needs the peer's packets of operation s+1, which the peer sends
+// only after finishing s), so parity s is free again when s+2 writes it.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void st_ll(char* p, u32 a, u32 b, u32 flag) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(flag), "r"(b), "r"(flag));
+}
+__device__ __forceinline__ uint4 ld_ll(const char* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+template <typename T, bool SUM, int NCTX>
+__global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
+k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
+  const int ci = ctx_index<NCTX>();
+  const RankCtx& c = pk.ctx[ci];
+  const RankBufs& ub = pk.buf[ci];
+  const int N = c.world, r = c.rank;
+  const volatile LocalState* st = c.state;
+  const u64 seq = st->ll_seq;
+  const u32 flag = (u32)(seq % 0xfffffffeull) + 1u;
+  const u64 par = (seq & 1) * (u64)kMaxRanks * kLLSlotBytes;
+  const Region src = make_region(ub.send, op.bytes), dst = make_region(ub.recv, op.bytes);
+  const bool als = region_aligned(src), ald = region_aligned(dst);
+  const u64 units = units_of(op.bytes);
+  u64 lo, hi;
+  block_span(units, units, lo, hi);
+  char* my_ll = c.stage[r] + c.ll_off + par;
+  for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
+    uint4 v[kMaxRanks];
+    const uint4 mine = region_ld(src, als, i);
+#pragma unroll
+    for (int k = 1; k < kMaxRanks; ++k) {
+      if (k < N) {
+        int p = r + k;
+        if (p >= N) p -= N;
+        char* d = c.stage[p] + c.ll_off + par + (u64)r * kLLSlotBytes + i * 32;
+        st_ll(d, mine.x, mine.y, flag);
+        st_ll(d + 16, mine.z, mine.w, flag);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kMaxRanks; ++k) {
+      if (k < N) {
+        if (k == r) {
+          v[k] = mine;
+        } else {
+          const char* s = my_ll + (u64)k * kLLSlotBytes + i * 32;
+          uint4 a = ld_ll(s), b = ld_ll(s + 16);
+          u32 spins = 0;
+          u64 t0 = 0;
+          while (a.y != flag || a.w != flag || b.y != flag || b.w != flag) {
+            a = ld_ll(s);
+            b = ld_ll(s + 16);
+            if ((++spins & 0xFFFFu) == 0) {  // watchdog, as in wait_flag_slow
+              const u64 now = globaltimer_ns();
+              if (t0 == 0) t0 = now;
+              volatile HostMailbox* mb = c.mbox;
+              if (mb->abort) { mb->error = 5; break; }
+              if (c.timeout_ns != 0 && now - t0 > c.timeout_ns) { mb->error = 4; break; }
+            }
+          }
+          v[k] = make_uint4(a.x, a.z, b.x, b.z);
+        }
+      }
+    }
+    Reducer<T> R;
+    R.init(v[0]);
+#pragma unroll
+    for (int k = 1; k < kMaxRanks; ++k)
+      if (k < N) R.template add<SUM>(v[k], op.op);
+    region_st(dst, ald, i, R.result(op.avg, N));
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    LocalState* s = c.state;
+    const u32 prev = atomicAdd(&s->done, 1u);
+    if (prev == gridDim.x - 1) {
+      s->done = 0;
+      s->ll_seq = seq + 1;
+      __threadfence();
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // all_reduce, two-shot: reduce-scatter into the shard owner, then every rank
 // pulls the reduced shards.  Wire bytes per GPU: (N-1)/N*S each way per phase.

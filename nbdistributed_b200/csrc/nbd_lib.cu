@@ -114,6 +114,7 @@ struct nbd_comm {
   uint64_t* imp_tmp = nullptr;                  // pinned ring of pointers handed to cudaMemcpyAsync
   int imp_tmp_n = 0;
   uint64_t t_host_chunk = 0;
+  uint64_t t_ll_max = 0;  // LL all_reduce up to this many bytes (tunable "ll_max_bytes"; 1 = off)
   HostPipe hp;
   uint64_t timeout_ms = 600000;
   const char* last_algo = "none";
@@ -169,6 +170,7 @@ static int alloc_rank(nbd_comm* c, size_t stage_bytes) {
   c->num_sms = prop.multiProcessorCount;
   NBD_CUDA(cudaMalloc((void**)&c->arena, c->arena_bytes));
   NBD_CUDA(cudaMemset(c->arena, 0, kFlagBytes));
+  NBD_CUDA(cudaMemset(c->arena + kFlagBytes + stage_bytes - kLLAreaBytes, 0, kLLAreaBytes));  // LL flags start at 0
   NBD_CUDA(cudaMalloc((void**)&c->state, sizeof(LocalBlock)));  // LocalState is its first member
   NBD_CUDA(cudaMemset(c->state, 0, sizeof(LocalBlock)));
   if (!c->emu) {
@@ -210,7 +212,9 @@ static void fill_ctx(nbd_comm* c) {
   }
   x.state = c->state;
   x.mbox = c->mbox_dev;
-  x.half_bytes = (c->stage_bytes / 2) / kUnit * kUnit;
+  // the last MiB of staging is the LL area; the two pipeline halves share the rest
+  x.ll_off = c->stage_bytes - kLLAreaBytes;
+  x.half_bytes = ((c->stage_bytes - kLLAreaBytes) / 2) / kUnit * kUnit;
   x.timeout_ns = c->timeout_ms * 1000000ull;
 }
 
@@ -425,6 +429,7 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "zc_ar_mode")) return &c->t_zc_fused;
   if (!strcmp(name, "zc_tile_bytes")) return &c->t_zc_tile;
   if (!strcmp(name, "host_chunk_bytes")) return &c->t_host_chunk;
+  if (!strcmp(name, "ll_max_bytes")) return &c->t_ll_max;
   if (!strcmp(name, "auto_register_off")) return &c->t_auto_off;
   if (!strcmp(name, "auto_min_bytes")) return &c->t_auto_min;
   return nullptr;
@@ -563,6 +568,19 @@ static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
   p.op.op = op;
   p.op.avg = (op == NBD_AVG);
   p.op.world = N;
+  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kLLMaxBytes;
+  if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= kLLMaxBytes) {
+    p.op.algo = 3;  // LL one-shot: packets carry their own flags, no barrier
+    p.op.chunk_bytes = bytes;
+    p.op.nchunks = 1;
+    u64 want = ceil_div(ceil_div(bytes, kUnit), (u64)kThreads);
+    u64 cap = emu_world > 1 ? (u64)c->num_sms / emu_world : 8;
+    if (cap > 8) cap = 8;
+    if (cap < 1) cap = 1;
+    p.nblocks = (int)(want < 1 ? 1 : (want < cap ? want : cap));
+    c->last_algo = "ar_ll";
+    return p;
+  }
   if (bytes <= ar1_max) {
     p.op.algo = 1;
     u64 cap = floor_to(half / N, kUnit);
@@ -681,13 +699,14 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
     default: rc = fail(NBD_ERR_UNSUPPORTED, "dtype %d cannot be reduced", dtype); \
   }
 
-enum Kind { K_AR1, K_AR2, K_RS };
+enum Kind { K_AR1, K_AR2, K_RS, K_LL };
 
 template <typename T, bool SUM, int NCTX>
 static const void* reduce_kernel(Kind k) {
   switch (k) {
     case K_AR1: return (const void*)k_allreduce_oneshot<T, SUM, NCTX>;
     case K_AR2: return (const void*)k_allreduce_twoshot<T, SUM, NCTX>;
+    case K_LL: return (const void*)k_allreduce_ll<T, SUM, NCTX>;
     default: return (const void*)k_reduce_scatter<T, SUM, NCTX>;
   }
 }
@@ -1050,7 +1069,7 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
   Plan p = plan_all_reduce(c, bytes, op, 0);
   Pack<1> pk;
   fill_pack(pk, c, send, recv);
-  return launch_reduce<1>(p.op.algo == 1 ? K_AR1 : K_AR2, dtype, op, p.nblocks, 1, s, pk, &p.op);
+  return launch_reduce<1>(p.op.algo == 3 ? K_LL : (p.op.algo == 1 ? K_AR1 : K_AR2), dtype, op, p.nblocks, 1, s, pk, &p.op);
 }
 
 int nbd_reduce_scatter(nbd_comm_t c, const void* send, void* recv, size_t recv_count, int dtype, int op,
@@ -1252,7 +1271,8 @@ int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* re
   if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;
   Plan p = plan_all_reduce(c0, bytes, op, g->world);
   for (int r = 1; r < g->world; ++r) g->comms[r]->last_algo = c0->last_algo;
-  return launch_reduce<kMaxRanks>(p.op.algo == 1 ? K_AR1 : K_AR2, dtype, op, p.nblocks, g->world, s, pk, &p.op);
+  return launch_reduce<kMaxRanks>(p.op.algo == 3 ? K_LL : (p.op.algo == 1 ? K_AR1 : K_AR2), dtype, op, p.nblocks, g->world,
+                                  s, pk, &p.op);
 }
 
 int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends, void* const* recvs, size_t recv_count,

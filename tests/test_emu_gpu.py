@@ -152,13 +152,14 @@ def test_all_reduce_one_shot_pipelined(torch_cuda, groups, world):
                                       ("i32", "bor"), ("i32", "bxor"), ("i64", "max"), ("i64", "bxor"),
                                       ("u8", "max"), ("u8", "min"), ("i8", "min"), ("i8", "max"), ("u8", "bor"),
                                       ("i8", "prod")])
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "zerocopy"])
+@pytest.mark.parametrize("algo", ["ll", "oneshot", "twoshot", "zerocopy"])
 def test_all_reduce_other_ops(torch_cuda, groups, dtype, op, algo):
     world = 4
-    knobs = {"oneshot": {"zero_copy_off": 1}, "twoshot": {"zero_copy_off": 1, "ar1_max_bytes": 1024},
+    knobs = {"ll": {"zero_copy_off": 1}, "oneshot": {"zero_copy_off": 1, "ll_max_bytes": 1},
+             "twoshot": {"zero_copy_off": 1, "ar1_max_bytes": 1024, "ll_max_bytes": 1},
              "zerocopy": {"zc_min_bytes": 1}}[algo]
     with tuned(groups(world), **knobs) as grp:
-        x = O.make_inputs(world, 5000, dtype, scale=1.0)
+        x = O.make_inputs(world, 2000 if algo == "ll" else 5000, dtype, scale=1.0)
         got, _ = _run_all_reduce(torch_cuda, grp, x, dtype, op=op)
         assert grp.last_algo() == "ar_" + algo
         want = O.all_reduce(x, dtype, op)
@@ -479,3 +480,28 @@ def test_all_reduce_host_buffers(torch_cuda, groups, world, dtype, numel, chunk)
         grp.all_reduce_host(hin)  # in place
         torch.cuda.synchronize()
         H.assert_same(H.to_numpy(hin[0], dtype), want, dtype, "in place")
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_ll_all_reduce_back_to_back(torch_cuda, groups, world):
+    """The flag-in-data path: many small all_reduces in a row without host synchronisation
+    (buffer parity, sequence flags), mixed sizes and dtypes, in place and out of place."""
+    torch = torch_cuda
+    grp = groups(world)
+    rng = np.random.default_rng(3)
+    runs = []
+    for it in range(60):
+        dtype = ("f32", "bf16", "i64", "u8")[it % 4]
+        n = int(rng.integers(1, (32 << 10) // O.NP_DTYPE[dtype]().itemsize))
+        x = O.make_inputs(world, n, dtype, seed=it)
+        t = [H.to_cuda(a, dtype) for a in x]
+        out = t if it % 3 else [torch.empty_like(a) for a in t]
+        grp.all_reduce(t, out)
+        assert grp.last_algo() == "ar_ll"
+        runs.append((x, out, dtype))
+    torch.cuda.synchronize()
+    grp.async_error()
+    for i, (x, out, dtype) in enumerate(runs):
+        want = O.reduce_rank_order(x, dtype)
+        for r in range(world):
+            H.assert_same(H.to_numpy(out[r], dtype), want, dtype, f"op {i} rank {r}")

@@ -102,14 +102,29 @@ __device__ __forceinline__ void reduce_units(const RankCtx& c, const Region& own
                                              u64 slot_stride, const Region& dst, char* stage_out, u64 lo,
                                              u64 hi, int op, int avg) {
   const int N = c.world, r = c.rank;
-  const bool als = region_aligned(own_src), ald = region_aligned(dst);
+  const u64 fs = fast_units(own_src), fd = fast_units(dst);
+  const u64 f = fs < fd ? fs : fd;
+  const u64 fh = hi < f ? hi : (lo > f ? lo : f);
+  const char* sp = own_src.p;
+  char* dp = dst.p;
+  // hot loop: plain 128-bit accesses only
   reduce_loop<T, SUM, true>(
-      N, lo, hi, op, avg,
-      [&](int k, u64 i) { return (k == r) ? region_ld(own_src, als, i) : ld16(slots + (u64)k * slot_stride + i * kUnit); },
+      N, lo, fh, op, avg,
+      [&](int k, u64 i) { return (k == r) ? ld16(sp + i * kUnit) : ld16(slots + (u64)k * slot_stride + i * kUnit); },
       [&](u64 i, const uint4& out) {
-        region_st(dst, ald, i, out);
+        st16(dp + i * kUnit, out);
         if (TO_STAGE) st16(stage_out + i * kUnit, out);
       });
+  if (fh < hi) {  // ragged last unit / misaligned user memory
+    const bool als = region_aligned(own_src), ald = region_aligned(dst);
+    reduce_loop_u<T, SUM, 1>(
+        N, fh, hi, op, avg,
+        [&](int k, u64 i) { return (k == r) ? region_ld(own_src, als, i) : ld16(slots + (u64)k * slot_stride + i * kUnit); },
+        [&](u64 i, const uint4& out) {
+          region_st(dst, ald, i, out);
+          if (TO_STAGE) st16(stage_out + i * kUnit, out);
+        });
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -620,35 +635,36 @@ k_allreduce_zc(const __grid_constant__ PackZc<NCTX> pk, const OpParams op) {
 #pragma unroll
   for (int k = 0; k < kMaxRanks; ++k)
     if (k < N) al = al && ((reinterpret_cast<uintptr_t>(z.send[k]) | reinterpret_cast<uintptr_t>(z.recv[k])) & (kUnit - 1)) == 0;
+  // [first+lo, fh): whole units of aligned buffers -> plain 128-bit accesses, no per-access
+  // checks in the hot loop; [fh, first+hi): ragged last unit or misaligned buffers (checked)
+  const u64 full = al ? op.bytes / kUnit : 0;
+  const u64 a0 = first + lo, b0 = first + hi;
+  const u64 fh = b0 < full ? b0 : (a0 > full ? a0 : full);
+  auto push_all = [&](u64 i, const uint4& out) {
+#pragma unroll
+    for (int k = 0; k < kMaxRanks; ++k) {
+      if (k < N) {
+        int p = r + k;  // own buffer first, then peers in rotated order
+        if (p >= N) p -= N;
+        st16(z.recv[p] + i * kUnit, out);
+      }
+    }
+  };
   if (op.algo == 0) {
     // fused: every unit is reduced and immediately written to all N buffers
-    reduce_loop<T, SUM, false>(
-        N, first + lo, first + hi, op.op, op.avg,
-        [&](int k, u64 i) { return region_ld(make_region(z.send[k], op.bytes), al, i); },
-        [&](u64 i, const uint4& out) {
-#pragma unroll
-          for (int k = 0; k < kMaxRanks; ++k) {
-            if (k < N) {
-              int p = r + k;  // own buffer first, then peers in rotated order
-              if (p >= N) p -= N;
-              region_st(make_region(z.recv[p], op.bytes), al, i, out);
-            }
-          }
-        });
+    reduce_loop<T, SUM, false>(N, a0, fh, op.op, op.avg, [&](int k, u64 i) { return ld16(z.send[k] + i * kUnit); }, push_all);
   } else {
     // tiled: reduce a tile of the span into our own recv (remote reads only), then push that
     // tile to the peers (remote writes only).  Loops that only read or only write remote
     // memory sustain more NVLink bandwidth than one loop doing both (632 / 667 vs 557 GB/s
     // at N = 8); the tile is re-read from L2.  chunk_bytes = tile bytes (0: the whole span).
-    const u64 tile = op.chunk_bytes ? (op.chunk_bytes / kUnit + kThreads - 1) / kThreads * kThreads : (hi - lo);
-    const Region mine_out = make_region(z.recv[r], op.bytes);
+    const u64 tile = op.chunk_bytes ? (op.chunk_bytes / kUnit + kThreads - 1) / kThreads * kThreads : (fh - a0);
+    char* mine_out = z.recv[r];
 #pragma unroll 1
-    for (u64 t0 = first + lo; t0 < first + hi; t0 += (tile ? tile : 1)) {
-      const u64 t1 = (t0 + tile < first + hi) ? t0 + tile : first + hi;
-      reduce_loop<T, SUM, true>(
-          N, t0, t1, op.op, op.avg,
-          [&](int k, u64 i) { return region_ld(make_region(z.send[k], op.bytes), al, i); },
-          [&](u64 i, const uint4& out) { region_st(mine_out, al, i, out); });
+    for (u64 t0 = a0; t0 < fh; t0 += (tile ? tile : 1)) {
+      const u64 t1 = (t0 + tile < fh) ? t0 + tile : fh;
+      reduce_loop<T, SUM, true>(N, t0, t1, op.op, op.avg, [&](int k, u64 i) { return ld16(z.send[k] + i * kUnit); },
+                                [&](u64 i, const uint4& out) { st16(mine_out + i * kUnit, out); });
       __syncthreads();  // the tile is complete in our recv before any thread forwards it
 #pragma unroll 1
       for (u64 base = t0; base < t1; base += 4ull * kThreads) {
@@ -657,10 +673,19 @@ k_allreduce_zc(const __grid_constant__ PackZc<NCTX> pk, const OpParams op) {
         for (int k = 1; k < N; ++k) {
           int p = r + k;
           if (p >= N) p -= N;
-          copy_region_to_region<4>(make_region(z.recv[p], op.bytes), mine_out, base, bhi);
+          char* dp = z.recv[p];
+          copy_units<4>(base, bhi, [&](u64 i) { return ld16(mine_out + i * kUnit); },
+                        [&](u64 i, const uint4& v) { st16(dp + i * kUnit, v); });
         }
       }
     }
+  }
+  if (fh < b0) {
+    reduce_loop_u<T, SUM, 1>(
+        N, fh, b0, op.op, op.avg, [&](int k, u64 i) { return region_ld(make_region(z.send[k], op.bytes), al, i); },
+        [&](u64 i, const uint4& out) {
+          for (int k = 0; k < N; ++k) region_st(make_region(z.recv[k], op.bytes), al, i, out);
+        });
   }
   flag_barrier(c, ++clk.epoch);
   kernel_end(c, 2, 0);
@@ -690,10 +715,17 @@ k_reduce_scatter_zc(const __grid_constant__ PackZc<NCTX> pk, const OpParams op) 
 #pragma unroll
   for (int k = 0; k < kMaxRanks; ++k)
     if (k < N) als = als && region_aligned(make_region(z.send[k] + (u64)r * op.bytes, op.bytes));
-  reduce_loop<T, SUM, true>(
-      N, lo, hi, op.op, op.avg,
-      [&](int k, u64 i) { return region_ld(make_region(z.send[k] + (u64)r * op.bytes, op.bytes), als, i); },
-      [&](u64 i, const uint4& out) { region_st(dst, ald, i, out); });
+  const u64 full = (als && ald) ? op.bytes / kUnit : 0;
+  const u64 fh = hi < full ? hi : (lo > full ? lo : full);
+  const u64 soff = (u64)r * op.bytes;
+  char* dp = dst.p;
+  reduce_loop<T, SUM, true>(N, lo, fh, op.op, op.avg, [&](int k, u64 i) { return ld16(z.send[k] + soff + i * kUnit); },
+                            [&](u64 i, const uint4& out) { st16(dp + i * kUnit, out); });
+  if (fh < hi)
+    reduce_loop_u<T, SUM, 1>(
+        N, fh, hi, op.op, op.avg,
+        [&](int k, u64 i) { return region_ld(make_region(z.send[k] + soff, op.bytes), als, i); },
+        [&](u64 i, const uint4& out) { region_st(dst, ald, i, out); });
   flag_barrier(c, ++clk.epoch);  // nobody may overwrite its send buffer before all have read it
   kernel_end(c, 2, 0);
 }

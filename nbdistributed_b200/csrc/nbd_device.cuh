@@ -192,7 +192,7 @@ __device__ __forceinline__ u64 globaltimer_ns() {
 
 // Spin until *f >= epoch (flags only ever grow).  Gives up on abort/timeout and
 // records why in the host mailbox; the communicator is dead after that.
-__device__ __noinline__ void wait_flag_slow(HostMailbox* mbox, u64 timeout_ns, const u64* f,
+static __device__ __noinline__ void wait_flag_slow(HostMailbox* mbox, u64 timeout_ns, const u64* f,
                                             u64 epoch) {
   u64 t0 = 0;
   u32 spins = 0;
@@ -286,7 +286,7 @@ __device__ __forceinline__ Region make_region(const void* p, u64 n) {
 
 __device__ __forceinline__ u64 units_of(u64 bytes) { return (bytes + kUnit - 1) / kUnit; }
 
-__device__ __noinline__ uint4 region_ld_slow(const char* rp, u64 rn, u64 i) {
+static __device__ __noinline__ uint4 region_ld_slow(const char* rp, u64 rn, u64 i) {
   uint4 v = make_uint4(0, 0, 0, 0);
   const u64 off = i * kUnit;
   const volatile unsigned char* s = reinterpret_cast<const volatile unsigned char*>(rp) + off;
@@ -299,7 +299,7 @@ __device__ __noinline__ uint4 region_ld_slow(const char* rp, u64 rn, u64 i) {
   return v;
 }
 
-__device__ __noinline__ void region_st_slow(char* rp, u64 rn, u64 i, uint4 v) {
+static __device__ __noinline__ void region_st_slow(char* rp, u64 rn, u64 i, uint4 v) {
   const u64 off = i * kUnit;
   volatile unsigned char* d = reinterpret_cast<volatile unsigned char*>(rp) + off;
   const u32 w[4] = {v.x, v.y, v.z, v.w};

@@ -786,7 +786,7 @@ struct AgreeArgs {
   int need;
 };
 
-__global__ void __launch_bounds__(64, 1) k_zc_agree(const __grid_constant__ Pack<1> pk, const AgreeArgs a) {
+static __global__ void __launch_bounds__(64, 1) k_zc_agree(const __grid_constant__ Pack<1> pk, const AgreeArgs a) {
   const RankCtx& c = pk.ctx[0];
   const int N = c.world, r = c.rank, t = threadIdx.x;
   LocalBlock* blk = reinterpret_cast<LocalBlock*>(c.state);

@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "../../include/nbdist_b200.h"
+#include "nbd_kernel_table.h"
 #include "nbd_kernels.cuh"
 
 using namespace nbd;
@@ -686,31 +687,6 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
 // ---------------------------------------------------------------------------
 // launch
 // ---------------------------------------------------------------------------
-#define NBD_SWITCH_DTYPE(dtype, ...)                                         \
-  switch (dtype) {                                                           \
-    case NBD_F32: { typedef float T; __VA_ARGS__; } break;                   \
-    case NBD_BF16: { typedef __nv_bfloat16 T; __VA_ARGS__; } break;          \
-    case NBD_F16: { typedef __half T; __VA_ARGS__; } break;                  \
-    case NBD_F64: { typedef double T; __VA_ARGS__; } break;                  \
-    case NBD_I32: { typedef int32_t T; __VA_ARGS__; } break;                 \
-    case NBD_I64: { typedef int64_t T; __VA_ARGS__; } break;                 \
-    case NBD_U8: { typedef uint8_t T; __VA_ARGS__; } break;                  \
-    case NBD_I8: { typedef int8_t T; __VA_ARGS__; } break;                   \
-    default: rc = fail(NBD_ERR_UNSUPPORTED, "dtype %d cannot be reduced", dtype); \
-  }
-
-enum Kind { K_AR1, K_AR2, K_RS, K_LL };
-
-template <typename T, bool SUM, int NCTX>
-static const void* reduce_kernel(Kind k) {
-  switch (k) {
-    case K_AR1: return (const void*)k_allreduce_oneshot<T, SUM, NCTX>;
-    case K_AR2: return (const void*)k_allreduce_twoshot<T, SUM, NCTX>;
-    case K_LL: return (const void*)k_allreduce_ll<T, SUM, NCTX>;
-    default: return (const void*)k_reduce_scatter<T, SUM, NCTX>;
-  }
-}
-
 template <int NCTX>
 static int launch_any(const void* kernel, int nblocks, int world, cudaStream_t s, Pack<NCTX>& pk, OpParams* op) {
   void* args[2] = {(void*)&pk, (void*)op};
@@ -726,11 +702,10 @@ static int launch_any(const void* kernel, int nblocks, int world, cudaStream_t s
 template <int NCTX>
 static int launch_reduce(Kind k, int dtype, int op, int nblocks, int world, cudaStream_t s, Pack<NCTX>& pk,
                          OpParams* prm) {
-  int rc = NBD_OK;
   const bool sum = (op == NBD_SUM || op == NBD_AVG);
-  const void* fn = nullptr;
-  NBD_SWITCH_DTYPE(dtype, fn = sum ? reduce_kernel<T, true, NCTX>(k) : reduce_kernel<T, false, NCTX>(k));
-  if (rc != NBD_OK) return rc;
+  const void* fn = staged_reduce_kernel_float((int)k, dtype, sum, NCTX != 1);
+  if (!fn) fn = staged_reduce_kernel_int((int)k, dtype, sum, NCTX != 1);
+  if (!fn) return fail(NBD_ERR_UNSUPPORTED, "dtype %d cannot be reduced", dtype);
   return launch_any<NCTX>(fn, nblocks, world, s, pk, prm);
 }
 
@@ -797,13 +772,6 @@ static int find_reg(const nbd_comm* c, const void* ptr, u64 bytes, u64* off) {
   return -1;
 }
 
-enum ZKind { Z_AR, Z_RS };
-
-template <typename T, bool SUM, int NCTX>
-static const void* zc_reduce_kernel(ZKind k) {
-  return k == Z_AR ? (const void*)k_allreduce_zc<T, SUM, NCTX> : (const void*)k_reduce_scatter_zc<T, SUM, NCTX>;
-}
-
 static int launch_ptr(const void* kernel, int nblocks, int world, bool coop, cudaStream_t s, void* pk, OpParams* op) {
   void* args[2] = {pk, (void*)op};
   if (!coop) {
@@ -818,11 +786,9 @@ static int launch_ptr(const void* kernel, int nblocks, int world, bool coop, cud
 template <int NCTX>
 static int launch_zc_reduce(ZKind k, int dtype, int op, int nblocks, int world, cudaStream_t s, PackZc<NCTX>& pk,
                             OpParams* prm) {
-  int rc = NBD_OK;
   const bool sum = (op == NBD_SUM || op == NBD_AVG);
-  const void* fn = nullptr;
-  NBD_SWITCH_DTYPE(dtype, fn = sum ? zc_reduce_kernel<T, true, NCTX>(k) : zc_reduce_kernel<T, false, NCTX>(k));
-  if (rc != NBD_OK) return rc;
+  const void* fn = zc_reduce_kernel((int)k, dtype, sum, NCTX != 1);
+  if (!fn) return fail(NBD_ERR_UNSUPPORTED, "dtype %d cannot be reduced", dtype);
   return launch_ptr(fn, nblocks, world, NCTX != 1, s, &pk, prm);
 }
 

@@ -37,7 +37,7 @@ SYMBOLS = [
     "nbd_emu_all_reduce", "nbd_emu_broadcast", "nbd_emu_all_gather", "nbd_emu_reduce_scatter", "nbd_emu_barrier",
     "nbd_all_reduce_host", "nbd_emu_all_reduce_host",
     "nbd_local_all_reduce_noalloc",
-    "nbd_comm_last_zc_decision",
+    "nbd_comm_last_zc_decision", "nbd_plan_query",
     "nbd_launch_count", "nbd_last_algo",
 ]
 NOALLOC_MAX_BYTES = 1 << 20
@@ -99,6 +99,7 @@ def load() -> C.CDLL:
         "nbd_emu_all_reduce_host": (i, [vp, pp, pp, sz, i, i, vp]),
         "nbd_local_all_reduce_noalloc": (i, [pp, pp, i, sz, i, i, vp]),
         "nbd_comm_last_zc_decision": (i, [vp]),
+        "nbd_plan_query": (i, [i, sz, i, i, i, sz, C.POINTER(u64)]),
         "nbd_launch_count": (u64, []),
         "nbd_last_algo": (C.c_char_p, [vp]),
     }
@@ -119,6 +120,16 @@ def check(rc: int) -> None:
 
 def launch_count() -> int:
     return int(load().nbd_launch_count())
+
+
+def plan_query(world: int, kind: str, nbytes: int, stage_bytes: int = 0, num_sms: int = 148, emulated: bool = False) -> dict:
+    """The planner's choice for a collective (GPU-free): algorithm code, chunking, grid."""
+    lib = load()
+    out = (C.c_uint64 * 6)()
+    code = {"all_reduce": 0, "reduce_scatter": 1, "all_gather": 2, "broadcast": 3}[kind]
+    check(lib.nbd_plan_query(world, stage_bytes, num_sms, int(emulated), code, nbytes, out))
+    return {"algo": int(out[0]), "chunk_bytes": int(out[1]), "nchunks": int(out[2]), "nblocks": int(out[3]),
+            "half_bytes": int(out[4]), "ll_off": int(out[5])}
 
 
 def torch_dtype_code(dtype) -> int:

@@ -1661,3 +1661,38 @@ extern "C" int nbd_emu_all_reduce_host(nbd_comm_t any, const void* const* host_s
     return nbd_emu_all_reduce(any, sends, recvs, (size_t)(n / es), dtype, op, s);
   });
 }
+
+// ---------------------------------------------------------------------------
+// nbd_plan_query — which algorithm / chunking / grid the planner picks, without a GPU
+// ---------------------------------------------------------------------------
+// kind: 0 all_reduce, 1 reduce_scatter (bytes = one shard), 2 all_gather (bytes = one shard),
+// 3 broadcast.  out: {algo, chunk_bytes, nchunks, nblocks, half_bytes, ll_off}.
+extern "C" int nbd_plan_query(int world, size_t stage_bytes, int num_sms, int emu, int kind, size_t bytes, uint64_t* out) {
+  if (!out || world < 2 || world > kMaxRanks || num_sms < 1) return fail(NBD_ERR_INVALID_ARGUMENT, "bad plan query");
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lk(mu);
+  nbd_comm c;  // planning record only: no device memory is touched
+  c.world = world;
+  c.num_sms = num_sms;
+  c.emu = emu != 0;
+  if (stage_bytes == 0) stage_bytes = kDefaultStage;
+  c.stage_bytes = (stage_bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
+  c.ctx.ll_off = c.stage_bytes - kLLAreaBytes;
+  c.ctx.half_bytes = ((c.stage_bytes - kLLAreaBytes) / 2) / kUnit * kUnit;
+  Plan p;
+  const int ew = emu ? world : 0;
+  switch (kind) {
+    case 0: p = plan_all_reduce(&c, bytes, NBD_SUM, ew); break;
+    case 1: p = plan_reduce_scatter(&c, bytes, NBD_SUM, ew); break;
+    case 2: p = plan_all_gather(&c, bytes, ew); break;
+    case 3: p = plan_broadcast(&c, bytes, 0, ew); break;
+    default: return fail(NBD_ERR_INVALID_ARGUMENT, "unknown collective kind %d", kind);
+  }
+  out[0] = (uint64_t)p.op.algo;
+  out[1] = p.op.chunk_bytes;
+  out[2] = p.op.nchunks;
+  out[3] = (uint64_t)p.nblocks;
+  out[4] = c.ctx.half_bytes;
+  out[5] = c.ctx.ll_off;
+  return NBD_OK;
+}

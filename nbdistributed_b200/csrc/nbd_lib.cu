@@ -860,10 +860,11 @@ static bool auto_wanted(const nbd_comm* c, u64 bytes) {
          bytes >= (c->t_auto_min ? c->t_auto_min : kDefAutoMin);
 }
 
-// all_reduce: with more than two ranks the staged two-shot is already within 3 % of zero-copy
-// (8xB200, 256 MiB: 579 vs 578 GB/s), so the agreement only pays for itself on larger messages
+// all_reduce: at 8 ranks the staged two-shot is already within 3 % of zero-copy (256 MiB: 579 vs
+// 578 GB/s), so the agreement only pays for itself on very large messages; at 4 ranks zero-copy
+// is far ahead (1 GiB: 670 GB/s vs 460 GB/s staged at 256 MiB; profiles/r01_bench_n4_*.json)
 static bool auto_wanted_ar(const nbd_comm* c, u64 bytes) {
-  return auto_wanted(c, bytes) && (c->t_auto_min || c->world <= 2 || bytes >= (512ull << 20));
+  return auto_wanted(c, bytes) && (c->t_auto_min || c->world <= 4 || bytes >= (512ull << 20));
 }
 
 struct ExportRef {

@@ -225,17 +225,16 @@ def run_ours_single(args):
     per_rank = S * bus_factor(R) / (ms * 1e-3) / 1e9
     value = per_rank * R
 
-    # correctness of what was timed: spot-check against the oracle (rank order, bit-exact)
-    import numpy as np
-
-    from oracle import collectives_oracle as O
-
-    idx = torch.from_numpy(np.random.default_rng(0).integers(0, numel, 8192)).to(dev)
-    sample = [s[idx].cpu().numpy() for s in sends]
-    want = O.reduce_rank_order(sample, "f32")
+    # correctness of what was timed: a sample re-reduced with plain fp32 adds in the kernels' fixed
+    # order (ascending rank) must match bit for bit on the first and the last rank.  (The oracle
+    # under oracle/ is only used by the cpu_baseline / --impl reference legs of this file.)
+    idx = torch.randint(0, numel, (8192,), device=dev, generator=g)
+    want = sends[0][idx].clone()
+    for r in range(1, R):
+        want = want + sends[r][idx]
     for r in (0, R - 1):
-        if not np.array_equal(recvs[r][idx].cpu().numpy().view(np.uint32), want.view(np.uint32)):
-            raise SystemExit("bench.py: timed all_reduce does not match the oracle")
+        if not torch.equal(recvs[r][idx].view(torch.int32), want.view(torch.int32)):
+            raise SystemExit("bench.py: the timed all_reduce does not match a rank-order fp32 re-reduction")
 
     # ---- end to end: pinned host buffers -> H2D -> all_reduce -> D2H, every step --------
     host_in = [torch.empty(numel, dtype=torch.float32).pin_memory() for _ in range(R)]

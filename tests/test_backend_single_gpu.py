@@ -41,3 +41,46 @@ def test_world_size_one_through_torch_distributed():
     from oracle.gloo_runner import free_port
 
     _run_world1(free_port())
+
+
+def _run_world1_cuda_only(port):
+    """Backend string without a CPU half: dist.barrier() is then routed to BackendB200::barrier
+    (with "cpu:gloo,cuda:b200" Python sends a device-less barrier to gloo)."""
+    import torch
+    import torch.distributed as dist
+
+    from nbdistributed_b200 import backend as B
+    from nbdistributed_b200 import worker_init as W
+
+    ns = W.init_worker(0, 1, "127.0.0.1", port, gpu_id=0, backend="cuda:b200")
+    try:
+        assert ns["__backend__"] == "cuda:b200"
+        dist.barrier()                      # -> our backend (current CUDA device)
+        dist.barrier(device_ids=[0])
+        x = torch.ones(4096, device="cuda:0")
+        dist.all_reduce(x)
+        assert float(x.sum()) == 4096.0
+        h = torch.arange(1 << 20, dtype=torch.float32).pin_memory()
+        out = torch.empty_like(h).pin_memory()
+        B.all_reduce_host(h, out=out)       # host-buffer pipeline at world size 1: a copy through the GPU
+        assert torch.equal(out, h)
+        sym = B.empty_symmetric(1 << 16, torch.bfloat16)
+        sym.fill_(2.0)
+        dist.all_reduce(sym)
+        assert float(sym[0]) == 2.0
+        del sym
+    finally:
+        W.shutdown_worker()
+
+
+def test_cuda_only_backend_string_routes_barrier_to_b200():
+    import multiprocessing as mp
+
+    from oracle.gloo_runner import free_port
+
+    # a fresh process: the default process group of this interpreter was already used above
+    ctx = mp.get_context("spawn")
+    p = ctx.Process(target=_run_world1_cuda_only, args=(free_port(),))
+    p.start()
+    p.join(timeout=180)
+    assert p.exitcode == 0

@@ -361,43 +361,64 @@ __device__ __forceinline__ void copy_units(u64 lo, u64 hi, LD ld, ST st) {
   }
 }
 
+// NOTE: the three helpers below keep the per-access checked form on purpose.  Splitting them
+// into an unchecked hot loop plus a checked tail (as the zero-copy kernels do with copy_units)
+// raised the register pressure of k_allreduce_twoshot (stack 200 -> 328 B) and cost the staged
+// two-shot all_reduce 18 % at 8xB200 (256 MiB: 574 -> 471 GB/s, profiles/r01_bench_n8_*.json).
 // Copy units [lo,hi): user region -> staging (dst may be a peer's arena).
 template <int U>
 __device__ __forceinline__ void copy_region_to_stage(char* dst, const Region& src, u64 lo, u64 hi) {
-  const u64 f = fast_units(src);
-  const u64 fh = hi < f ? hi : (lo > f ? lo : f);
-  const char* sp = src.p;
-  copy_units<U>(lo, fh, [&](u64 i) { return ld16(sp + i * kUnit); }, [&](u64 i, const uint4& v) { st16(dst + i * kUnit, v); });
-  if (fh < hi)
-    copy_units<1>(fh, hi, [&](u64 i) { return region_ld_slow(src.p, src.n, i); },
-                  [&](u64 i, const uint4& v) { st16(dst + i * kUnit, v); });
+  const bool al = region_aligned(src);
+  for (u64 base = lo + threadIdx.x; base < hi; base += (u64)U * kThreads) {
+    uint4 v[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kThreads;
+      if (i < hi) v[j] = region_ld(src, al, i);
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kThreads;
+      if (i < hi) st16(dst + i * kUnit, v[j]);
+    }
+  }
 }
 
 // Copy units [lo,hi): staging (maybe a peer's) -> user region.
 template <int U>
 __device__ __forceinline__ void copy_stage_to_region(const Region& dst, const char* src, u64 lo, u64 hi) {
-  const u64 f = fast_units(dst);
-  const u64 fh = hi < f ? hi : (lo > f ? lo : f);
-  char* dp = dst.p;
-  copy_units<U>(lo, fh, [&](u64 i) { return ld16(src + i * kUnit); }, [&](u64 i, const uint4& v) { st16(dp + i * kUnit, v); });
-  if (fh < hi)
-    copy_units<1>(fh, hi, [&](u64 i) { return ld16(src + i * kUnit); },
-                  [&](u64 i, const uint4& v) { region_st_slow(dst.p, dst.n, i, v); });
+  const bool al = region_aligned(dst);
+  for (u64 base = lo + threadIdx.x; base < hi; base += (u64)U * kThreads) {
+    uint4 v[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kThreads;
+      if (i < hi) v[j] = ld16(src + i * kUnit);
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kThreads;
+      if (i < hi) region_st(dst, al, i, v[j]);
+    }
+  }
 }
 
-// Copy units [lo,hi): user region -> user region.
+// Copy units [lo,hi): user region -> user region (both local).
 template <int U>
 __device__ __forceinline__ void copy_region_to_region(const Region& dst, const Region& src, u64 lo, u64 hi) {
-  const u64 fs = fast_units(src), fd = fast_units(dst);
-  const u64 f = fs < fd ? fs : fd;
-  const u64 fh = hi < f ? hi : (lo > f ? lo : f);
-  const char* sp = src.p;
-  char* dp = dst.p;
-  copy_units<U>(lo, fh, [&](u64 i) { return ld16(sp + i * kUnit); }, [&](u64 i, const uint4& v) { st16(dp + i * kUnit, v); });
-  if (fh < hi) {
-    const bool als = region_aligned(src), ald = region_aligned(dst);
-    copy_units<1>(fh, hi, [&](u64 i) { return region_ld(src, als, i); },
-                  [&](u64 i, const uint4& v) { region_st(dst, ald, i, v); });
+  const bool als = region_aligned(src), ald = region_aligned(dst);
+  for (u64 base = lo + threadIdx.x; base < hi; base += (u64)U * kThreads) {
+    uint4 v[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kThreads;
+      if (i < hi) v[j] = region_ld(src, als, i);
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kThreads;
+      if (i < hi) region_st(dst, ald, i, v[j]);
+    }
   }
 }
 

@@ -102,29 +102,14 @@ __device__ __forceinline__ void reduce_units(const RankCtx& c, const Region& own
                                              u64 slot_stride, const Region& dst, char* stage_out, u64 lo,
                                              u64 hi, int op, int avg) {
   const int N = c.world, r = c.rank;
-  const u64 fs = fast_units(own_src), fd = fast_units(dst);
-  const u64 f = fs < fd ? fs : fd;
-  const u64 fh = hi < f ? hi : (lo > f ? lo : f);
-  const char* sp = own_src.p;
-  char* dp = dst.p;
-  // hot loop: plain 128-bit accesses only
+  const bool als = region_aligned(own_src), ald = region_aligned(dst);
   reduce_loop<T, SUM, true>(
-      N, lo, fh, op, avg,
-      [&](int k, u64 i) { return (k == r) ? ld16(sp + i * kUnit) : ld16(slots + (u64)k * slot_stride + i * kUnit); },
+      N, lo, hi, op, avg,
+      [&](int k, u64 i) { return (k == r) ? region_ld(own_src, als, i) : ld16(slots + (u64)k * slot_stride + i * kUnit); },
       [&](u64 i, const uint4& out) {
-        st16(dp + i * kUnit, out);
+        region_st(dst, ald, i, out);
         if (TO_STAGE) st16(stage_out + i * kUnit, out);
       });
-  if (fh < hi) {  // ragged last unit / misaligned user memory
-    const bool als = region_aligned(own_src), ald = region_aligned(dst);
-    reduce_loop_u<T, SUM, 1>(
-        N, fh, hi, op, avg,
-        [&](int k, u64 i) { return (k == r) ? region_ld(own_src, als, i) : ld16(slots + (u64)k * slot_stride + i * kUnit); },
-        [&](u64 i, const uint4& out) {
-          region_st(dst, ald, i, out);
-          if (TO_STAGE) st16(stage_out + i * kUnit, out);
-        });
-  }
 }
 
 // ---------------------------------------------------------------------------

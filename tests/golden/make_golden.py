@@ -16,7 +16,7 @@ message (ref:src/nbdistributed/worker.py:395-418).  IPython is not installed in 
 
 /root/reference does not exist on the GPU box: only the .npz files travel.  Usage:
 
-    python tests/golden/make_golden.py            # writes tests/golden/ref_gloo_n{2,4}.npz
+    python tests/golden/make_golden.py            # writes tests/golden/ref_gloo_n{2,4,8}.npz
 """
 from __future__ import annotations
 
@@ -149,7 +149,7 @@ def main() -> None:
         extra = os.pathsep.join([stub, REF_SRC])
         os.environ["PYTHONPATH"] = extra + os.pathsep + os.environ.get("PYTHONPATH", "")
         sys.path[:0] = [stub, REF_SRC]
-        for world in (2, 4):
+        for world in (2, 4, 8):
             run_world(world, os.path.join(HERE, f"ref_gloo_n{world}.npz"))
 
 

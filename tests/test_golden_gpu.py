@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 OPCODE = {"sum": 0, "avg": 1, "prod": 2, "min": 3, "max": 4}
 
 
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("case", G.CASES, ids=[c.name for c in G.CASES])
 def test_cuda_reproduces_reference_outputs(world, case):
     import torch

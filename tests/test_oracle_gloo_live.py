@@ -1,4 +1,4 @@
-"""The oracle against a LIVE gloo group (the reference's CPU path), every run, N = 2 and 4."""
+"""The oracle against a LIVE gloo group (the reference's CPU path), every run, N = 2, 4 and 8."""
 import numpy as np
 import pytest
 
@@ -7,7 +7,7 @@ from oracle.gloo_runner import run_gloo
 from tests import helpers as H
 
 
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 def test_live_gloo_matches_oracle(world):
     jobs, meta = [], []
     for dtype, n in (("f32", 1), ("f32", 4096 + 5), ("bf16", 65536 + 13), ("f16", 1000), ("f64", 333), ("i64", 4097),

@@ -1,4 +1,4 @@
-"""The oracle against the reference's own outputs (golden fixtures, gloo path, N = 2 and 4)."""
+"""The oracle against the reference's own outputs (golden fixtures, gloo path, N = 2, 4 and 8)."""
 import numpy as np
 import pytest
 
@@ -7,7 +7,7 @@ from tests import golden_cases as G
 from tests import helpers as H
 
 
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("case", G.CASES, ids=[c.name for c in G.CASES])
 def test_oracle_reproduces_reference_outputs(world, case):
     data = G.load(world)

@@ -348,6 +348,146 @@ def _time_collective(torch, dist, fn, iters, warmup, cpu_group):
     return float(t.item())
 
 
+# --------------------------------------------------------------------------------------
+# parity of what is about to be timed, at the actual world size (driver-visible)
+# --------------------------------------------------------------------------------------
+def _seeded(torch, dev, rank, n, dtype, seed):
+    """Rank `rank`'s synthetic input: every process can regenerate every rank's tensor."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed + rank)
+    if dtype in (torch.int32, torch.int64):
+        return torch.randint(-(2 ** 30), 2 ** 30, (n,), generator=g, device=dev, dtype=dtype)
+    if dtype == torch.uint8:
+        return torch.randint(0, 256, (n,), generator=g, device=dev, dtype=torch.uint8)
+    return torch.randn(n, generator=g, device=dev, dtype=torch.float32).to(dtype)
+
+
+def _rank_order_sum(torch, dev, world, n, dtype, seed):
+    """Self-contained restatement of the kernels' fixed order (ascending rank; bf16 accumulates
+    in fp32 and is rounded once; integers wrap) - oracle/ stays out of the product arm."""
+    acc_t = torch.float32 if dtype in (torch.bfloat16, torch.float16) else dtype
+    acc = _seeded(torch, dev, 0, n, dtype, seed).to(acc_t)
+    for r in range(1, world):
+        acc = acc + _seeded(torch, dev, r, n, dtype, seed).to(acc_t)
+    return acc.to(dtype)
+
+
+def parity_check(torch, dist, dev, rank, world, cpu_group, be, B):
+    """All four collectives + barrier through dist.* on backend b200, every kernel family, checked
+    bit for bit against a rank-order re-reduction (integers and copies also against gloo through
+    the cpu group; float sums against gloo within the north_star tolerance)."""
+    cases, failed, algos, notes = 0, [], set(), []
+
+    def bits(t):
+        return t.contiguous().view(torch.uint8)
+
+    def check(name, ok):
+        nonlocal cases
+        cases += 1
+        algos.add(be.last_algo())
+        if not ok:
+            failed.append(f"{name} [{be.last_algo()}]")
+
+    def gloo_sum(x):
+        c = x.detach().cpu()
+        if c.dtype == torch.bfloat16:
+            c = c.float()  # compare magnitudes only; gloo's bf16 rounding differs by design
+        dist.all_reduce(c, group=cpu_group)
+        return c
+
+    eps = {torch.float32: 1e-6, torch.bfloat16: world * 2.0 ** -8}
+    # all_reduce: LL, one-shot, two-shot, auto-registered zero-copy
+    be.set_tunable("auto_min_bytes", 8 << 20)
+    for dtype, n in ((torch.float32, 1000), (torch.float32, 64 << 10), (torch.float32, (1 << 20) + 3),
+                     (torch.float32, 4 << 20), (torch.bfloat16, 4099), (torch.bfloat16, (2 << 20) + 8),
+                     (torch.int32, 70001), (torch.int64, 1 << 20)):
+        x = _seeded(torch, dev, rank, n, dtype, 4321)
+        want = _rank_order_sum(torch, dev, world, n, dtype, 4321)
+        reps = 3 if n * x.element_size() >= (8 << 20) else 1  # zero-copy takes over once peers imported the segment
+        for _ in range(reps):
+            y = x.clone()
+            dist.all_reduce(y)
+            check(f"all_reduce {dtype} n={n}", torch.equal(bits(y), bits(want)))
+        if dtype in (torch.int32, torch.int64):
+            check(f"all_reduce {dtype} n={n} vs gloo", torch.equal(y.cpu(), gloo_sum(x)))
+        elif n <= (1 << 20) + 3:
+            ref = gloo_sum(x).double()
+            mag = gloo_sum(x.abs()).double()
+            check(f"all_reduce {dtype} n={n} vs gloo (tolerance)", bool(((y.cpu().double() - ref).abs() <= eps[dtype] * mag + 1e-30).all()))
+    be.set_tunable("auto_min_bytes", 0)
+    # symmetric memory: zero-copy kernels
+    sym = B.empty_symmetric(2 << 20, torch.float32)
+    x = _seeded(torch, dev, rank, 2 << 20, torch.float32, 4400)
+    sym.copy_(x)
+    be.set_tunable("zc_min_bytes", 1 << 20)
+    dist.all_reduce(sym)
+    check("all_reduce on symmetric memory", torch.equal(bits(sym), bits(_rank_order_sum(torch, dev, world, 2 << 20, torch.float32, 4400))))
+    be.set_tunable("zc_min_bytes", 0)
+    del sym
+    # the tile pipeline over peer-to-peer transport
+    be.set_tunable("pipe", 1)
+    y = _seeded(torch, dev, rank, (3 << 20) + 5, torch.bfloat16, 4500)
+    dist.all_reduce(y)
+    check("all_reduce tile pipeline", torch.equal(bits(y), bits(_rank_order_sum(torch, dev, world, (3 << 20) + 5, torch.bfloat16, 4500))))
+    be.set_tunable("pipe", 0)
+    # broadcast: direct, scatter / multicast; first and last root
+    for n in (400, (1 << 20) + 17, (40 << 20) + 1):
+        for root in sorted({0, world - 1}):
+            y = _seeded(torch, dev, rank, n, torch.uint8, 4600 + root)
+            dist.broadcast(y, src=root)
+            check(f"broadcast {n}B root {root}", torch.equal(y, _seeded(torch, dev, root, n, torch.uint8, 4600 + root)))
+    # all_gather / reduce_scatter (tensor forms)
+    n = (1 << 20) + 8
+    x = _seeded(torch, dev, rank, n, torch.bfloat16, 4700)
+    out = torch.empty(world * n, dtype=torch.bfloat16, device=dev)
+    dist.all_gather_into_tensor(out, x)
+    check("all_gather_into_tensor", torch.equal(bits(out), bits(torch.cat([_seeded(torch, dev, r, n, torch.bfloat16, 4700) for r in range(world)]))))
+    n = 1 << 18
+    x = _seeded(torch, dev, rank, world * n, torch.float32, 4800)
+    o = torch.empty(n, dtype=torch.float32, device=dev)
+    dist.reduce_scatter_tensor(o, x)
+    want = _rank_order_sum(torch, dev, world, world * n, torch.float32, 4800)[rank * n:(rank + 1) * n]
+    check("reduce_scatter_tensor", torch.equal(bits(o), bits(want)))
+    dist.barrier(device_ids=[dev.index])
+    cases += 1
+    # NVSwitch multicast, where the box has it: copy exact, in-switch sums within tolerance,
+    # identical on all ranks, exact on integer-valued data
+    nv_on, nv_why = be.nvls_status()
+    notes.append(f"multicast: {'on' if nv_on else 'off'} ({nv_why})")
+    if nv_on:
+        be.set_tunable("nvls_reduce", 1)
+        n = (4 << 20) + 3
+        x = _seeded(torch, dev, rank, n, torch.float32, 4900)
+        y = x.clone()
+        dist.all_reduce(y)
+        want = _rank_order_sum(torch, dev, world, n, torch.float32, 4900)
+        mag = x.abs()
+        dist.all_reduce(mag)
+        check("in-switch all_reduce f32 (tolerance 1e-6 * sum|x|)", be.last_algo() == "ar_nvls" and
+              bool(((y.double() - want.double()).abs() <= 1e-6 * mag.double() + 1e-30).all()))
+        chk = y.view(torch.int32).sum(dtype=torch.int64).cpu().reshape(1)
+        allchk = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(allchk, chk, group=cpu_group)
+        check("in-switch all_reduce identical on all ranks", all(int(a) == int(allchk[0]) for a in allchk))
+        xi = _seeded(torch, dev, rank, n, torch.int32, 4950) % 1000
+        yi = xi.to(torch.float32)
+        dist.all_reduce(yi)
+        wi = xi.clone()
+        dist.all_reduce(wi)
+        check("in-switch all_reduce of integer-valued fp32 (exact)", torch.equal(yi, wi.to(torch.float32)))
+        be.set_tunable("nvls_reduce", 0)
+    torch.cuda.synchronize()
+    res = {"world": world, "cases": cases, "failed": len(failed), "algos": sorted(algos), "notes": notes}
+    if failed:
+        res["failures"] = failed[:8]
+    # every rank must agree that everything passed
+    flag = torch.tensor([len(failed)], dtype=torch.int64)
+    dist.all_reduce(flag, group=cpu_group)
+    res["failed_any_rank"] = int(flag.item())
+    return res
+
+
+
 def run_ours_multi(args):
     import torch
     import torch.distributed as dist
@@ -571,13 +711,13 @@ def run_reference(args):
         return None  # under torchrun only rank 0 works; the others exit 0
     n = max(1, args.gpus)
     ranks = EMU_RANKS if n == 1 else n
-    sample_bytes = min(MSG_BYTES, 64 << 20)
-    warm, iters = max(1, min(args.warmup, 3)), max(1, min(args.steps, 10))
+    sample_bytes = MSG_BYTES  # the same 256 MiB step as our arm; ~0.15 s per iteration on gloo
+    warm, iters = max(1, args.warmup), max(1, args.steps)
     t = gloo_cpu_baseline(ranks, sample_bytes, iters, warm)
     per_rank = sample_bytes * bus_factor(ranks) / t / 1e9
     value = round(per_rank * ranks, 3)
-    sample = (f"gloo all_reduce fp32 SUM, {sample_bytes >> 20} MiB per rank (bounded sample of the {MSG_BYTES >> 20} MiB "
-              f"step), {ranks} local processes over TCP loopback, {warm} warm-up + {iters} timed iterations")
+    sample = (f"gloo all_reduce fp32 SUM, {sample_bytes >> 20} MiB per rank (the full step of our arm), "
+              f"{ranks} local processes over TCP loopback, {warm} warm-up + {iters} timed iterations")
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n, "steps": iters, "warmup": warm,
         "ms_per_step": round(t * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -121,10 +121,27 @@ int nbd_comm_set_timeout_ms(nbd_comm_t comm, uint64_t timeout_ms);
 /* Tuning knobs: "blocks" (max CTAs per collective), "ar1_max_bytes"
  * (one-shot/two-shot all-reduce switch), "bcast_direct_max_bytes",
  * "chunk_bytes" (pipeline chunk), "zero_copy_off" (1 = always stage),
- * "zc_min_bytes" (smallest message that goes zero-copy).  value 0 restores
- * the default. */
+ * "zc_min_bytes" (smallest message that goes zero-copy), "nvls_reduce" (1 = float
+ * sums may be reduced in the NVSwitch), "nvls_off", "nvls_min_bytes", "pipe" (1 = use
+ * the tile-pipeline kernels over peer-to-peer transport), "pipe_tile_bytes".  value 0
+ * restores the default. */
 int nbd_comm_set_tunable(nbd_comm_t comm, const char* name, uint64_t value);
 int nbd_comm_get_tunable(nbd_comm_t comm, const char* name, uint64_t* value);
+
+/* NVSwitch multicast ("NVLS").  nbd_comm_connect also tries to bind a staging buffer of every
+ * rank (NBDIST_B200_NVLS_BYTES, default 128 MiB) into one multicast object, passing the handle
+ * between the processes over a unix socket that rank 0 names in its NBD handle; no extra
+ * rendezvous is asked of the caller.  If any rank cannot (no NVSwitch, driver without
+ * multicast, NBDIST_B200_NVLS=0) all ranks agree to run without it.  With it:
+ *   - nbd_broadcast of >= 512 KiB writes each tile once (multimem.st; the switch replicates it);
+ *   - nbd_all_reduce of f32/bf16/f16 SUM/AVG of >= 1 MiB is reduced INSIDE the switch
+ *     (multimem.ld_reduce) when the tunable "nvls_reduce" is 1 (or NBDIST_B200_NVLS_REDUCE=1).
+ *     Opt-in because the switch adds in an order of its own: results are identical on all ranks
+ *     and within the float tolerance of the rank-order result, but not bit-identical with it.
+ * Returns 1 if multicast is set up on this communicator, 0 if not (`why`, if given, receives
+ * a one-line reason), negative on error.  Replaces nothing in the reference; it is what
+ * backend "nccl" (ref:src/nbdistributed/worker.py:145) uses on the same hardware. */
+int nbd_comm_nvls_status(nbd_comm_t comm, char* why, size_t why_bytes);
 
 /* ---- symmetric memory (zero-copy collectives) --------------------------------
  * Replaces nothing in the reference; it is the backend side of c10d's

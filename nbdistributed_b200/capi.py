@@ -30,7 +30,7 @@ SYMBOLS = [
     "nbd_version", "nbd_error_string", "nbd_last_error", "nbd_dtype_size",
     "nbd_comm_create", "nbd_comm_get_handle", "nbd_comm_connect", "nbd_comm_destroy", "nbd_comm_abort",
     "nbd_comm_async_error", "nbd_comm_rank", "nbd_comm_world_size", "nbd_comm_set_timeout_ms",
-    "nbd_comm_set_tunable", "nbd_comm_get_tunable",
+    "nbd_comm_set_tunable", "nbd_comm_get_tunable", "nbd_comm_nvls_status",
     "nbd_mem_alloc", "nbd_mem_connect", "nbd_mem_free",
     "nbd_emu_create", "nbd_emu_destroy",
     "nbd_all_reduce", "nbd_broadcast", "nbd_all_gather", "nbd_reduce_scatter", "nbd_barrier",
@@ -80,6 +80,7 @@ def load() -> C.CDLL:
         "nbd_comm_set_timeout_ms": (i, [vp, u64]),
         "nbd_comm_set_tunable": (i, [vp, C.c_char_p, u64]),
         "nbd_comm_get_tunable": (i, [vp, C.c_char_p, C.POINTER(u64)]),
+        "nbd_comm_nvls_status": (i, [vp, C.c_char_p, sz]),
         "nbd_mem_alloc": (i, [vp, sz, pp, vp]),
         "nbd_mem_connect": (i, [vp, vp, vp]),
         "nbd_mem_free": (i, [vp, vp]),

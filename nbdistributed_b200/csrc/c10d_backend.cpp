@@ -490,6 +490,13 @@ class BackendB200 : public c10d::Backend {
   }
   std::string last_algo() { return comm_ ? nbd_last_algo(comm_) : "none"; }
   int last_zc_decision() { return comm_ ? nbd_comm_last_zc_decision(comm_) : -1; }
+  // (enabled, one-line reason): whether NVSwitch multicast was set up for this group
+  std::pair<bool, std::string> nvls_status() {
+    if (!comm_) return {false, "no communicator yet (created by the first collective)"};
+    char why[256] = "";
+    const int rc = nbd_comm_nvls_status(comm_, why, sizeof(why));
+    return {rc == 1, std::string(why)};
+  }
   int64_t device_index() const { return comm_ ? (int64_t)device_ : -1; }
   void set_inline_sync_ops(bool v) { inline_sync_ops_ = v; }
 
@@ -617,6 +624,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("set_tunable", &BackendB200::set_tunable)
       .def("last_algo", &BackendB200::last_algo)
       .def("last_zc_decision", &BackendB200::last_zc_decision)
+      .def("nvls_status", &BackendB200::nvls_status)
       .def("all_reduce_host", &BackendB200::all_reduce_host, py::arg("send"), py::arg("recv"), py::arg("op") = 0,
            py::call_guard<py::gil_scoped_release>())
       .def("repeat_all_reduce", &BackendB200::repeat_all_reduce, py::call_guard<py::gil_scoped_release>())

@@ -196,6 +196,12 @@ static __device__ __noinline__ void wait_flag_slow(HostMailbox* mbox, u64 timeou
                                             u64 epoch) {
   u64 t0 = 0;
   u32 spins = 0;
+  {
+    // a launch that already gave up once (timeout/abort) must drain, not wait a full timeout at
+    // every later flag: its results are void anyway and the communicator is dead
+    volatile HostMailbox* mb = mbox;
+    if (mb->error != 0) return;
+  }
   while (ld_relaxed_sys(f) < epoch) {
     if ((++spins & 0x3FFFu) == 0) {
       const u64 now = globaltimer_ns();

@@ -4,6 +4,8 @@
 // cudaLaunchKernel / cudaLaunchCooperativeKernel.
 #pragma once
 
+#include <stddef.h>
+
 namespace nbd {
 
 enum Kind { K_AR1, K_AR2, K_RS, K_LL };  // staged: one-shot, two-shot, reduce_scatter, LL
@@ -14,5 +16,10 @@ enum ZKind { Z_AR, Z_RS };               // zero-copy: all_reduce, reduce_scatte
 const void* staged_reduce_kernel_float(int kind, int dtype, bool sum, bool emu);
 const void* staged_reduce_kernel_int(int kind, int dtype, bool sum, bool emu);
 const void* zc_reduce_kernel(int zkind, int dtype, bool sum, bool emu);
+// tile-pipeline kernels (nbd_k_pipe.cu); mc: NVSwitch multicast transport (nullptr where the
+// switch cannot do the reduction); all need pipe_smem_bytes() of dynamic shared memory
+const void* pipe_allreduce_kernel(int dtype, bool sum, bool emu, bool mc);
+const void* pipe_broadcast_kernel(bool emu, bool mc);
+size_t pipe_smem_bytes();
 
 }  // namespace nbd

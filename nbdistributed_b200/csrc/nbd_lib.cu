@@ -20,123 +20,26 @@
 #include <string>
 #include <vector>
 
-#include "../../include/nbdist_b200.h"
+#include "nbd_host.h"
 #include "nbd_kernel_table.h"
 #include "nbd_kernels.cuh"
-
-using namespace nbd;
+#include "nbd_pipe.cuh"
 
 // ---------------------------------------------------------------------------
 // errors
 // ---------------------------------------------------------------------------
 static thread_local char g_last_error[512] = "";
-static std::atomic<uint64_t> g_launches{0};
+namespace nbd {
+std::atomic<uint64_t> g_launches{0};
 
-static int fail(int code, const char* fmt, ...) {
+int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
   va_end(ap);
   return code;
 }
-
-#define NBD_CUDA(call)                                                                      \
-  do {                                                                                      \
-    cudaError_t e__ = (call);                                                               \
-    if (e__ != cudaSuccess)                                                                 \
-      return fail(NBD_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
-                  __FILE__, __LINE__);                                                      \
-  } while (0)
-
-struct DeviceGuard {
-  int prev = -1;
-  bool changed = false;
-  explicit DeviceGuard(int dev) {
-    if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) changed = (cudaSetDevice(dev) == cudaSuccess);
-  }
-  ~DeviceGuard() {
-    if (changed) cudaSetDevice(prev);
-  }
-};
-
-// ---------------------------------------------------------------------------
-// communicator
-// ---------------------------------------------------------------------------
-struct EmuGroup;
-
-// Host-buffer collectives (nbd_*_host): three streams and a ring of device bounce buffers so
-// that the H2D copy of chunk k+1, the collective on chunk k and the D2H copy of chunk k-1
-// overlap; PCIe is full duplex, so a step costs ~max(H2D, D2H) instead of their sum.
-constexpr int kPipeSlots = 3;
-struct HostPipe {
-  bool ready = false;
-  int nranks = 0;        // 1 for a real rank, R for an emulated group
-  size_t chunk = 0;      // bytes per bounce buffer
-  cudaStream_t h2d = nullptr, comp = nullptr, d2h = nullptr;
-  cudaEvent_t ev_start = nullptr, ev_h2d[kPipeSlots] = {}, ev_comp[kPipeSlots] = {}, ev_d2h[kPipeSlots] = {};
-  bool used[kPipeSlots] = {};
-  char* buf[kMaxRanks][kPipeSlots] = {};
-};
-
-struct nbd_comm {
-  int rank = 0, world = 1, device = 0;
-  int num_sms = 0;
-  bool emu = false, connected = false, dead = false;
-  EmuGroup* group = nullptr;
-  char* arena = nullptr;
-  size_t arena_bytes = 0, stage_bytes = 0;
-  LocalState* state = nullptr;
-  HostMailbox* mbox = nullptr;      // host pointer (pinned, mapped)
-  HostMailbox* mbox_dev = nullptr;  // device alias
-  void* peer_base[kMaxRanks] = {};
-  RankCtx ctx = {};
-  // tunables (0 = default)
-  uint64_t t_blocks = 0, t_ar1_max = 0, t_bcast_direct_max = 0, t_chunk = 0;
-  uint64_t t_zc_off = 0, t_zc_min = 0;  // zero-copy switch / size threshold
-  uint64_t t_zc_fused = 0, t_zc_tile = 0;  // all_reduce: 1 = fused loop, 2 = tiled; tile bytes (0 = whole span)
-  struct Registration {                 // symmetric memory: same index on every rank
-    char* base = nullptr;
-    size_t bytes = 0;
-    void* peer[kMaxRanks] = {};
-    bool connected = false;
-  };
-  std::vector<Registration> regs;
-  // auto-registration of ordinary allocations (exports: ours; imports: peers')
-  uint64_t t_auto_off = 0, t_auto_min = 0;
-  ExportSlot* export_mirror = nullptr;          // pinned host copy of our export slots
-  int n_exports = 0;
-  std::map<uint64_t, int> export_of;            // buffer id -> slot
-  std::set<uint64_t> not_exportable;            // buffer ids cudaIpcGetMemHandle refused
-  std::set<uint64_t> imported;                  // (peer << 32 | slot) already mapped
-  std::vector<void*> import_ptrs;               // mappings to close at destroy
-  uint32_t miss_seen = 0;
-  cudaStream_t side = nullptr;                  // for reading peers' export slots
-  ExportSlot* import_tmp = nullptr;             // pinned scratch for one slot
-  uint64_t* imp_tmp = nullptr;                  // pinned ring of pointers handed to cudaMemcpyAsync
-  int imp_tmp_n = 0;
-  uint64_t t_host_chunk = 0;
-  uint64_t t_ll_max = 0;  // LL all_reduce up to this many bytes (tunable "ll_max_bytes"; 1 = off)
-  HostPipe hp;
-  uint64_t timeout_ms = 600000;
-  const char* last_algo = "none";
-};
-
-struct EmuGroup {
-  int world = 0;
-  nbd_comm* comms[kMaxRanks] = {};
-  HostPipe hp;
-};
-
-struct Handle {  // serialised into NBD_HANDLE_BYTES
-  uint32_t magic, version;
-  int32_t rank, world;
-  int64_t pid;
-  uint64_t hostid, arena_bytes, stage_bytes;
-  char pci[32];
-  cudaIpcMemHandle_t ipc;
-};
-static_assert(sizeof(Handle) <= NBD_HANDLE_BYTES, "handle too large");
-static const uint32_t kMagic = 0x4e424432u;  // "NBD2"
+}  // namespace nbd
 
 static uint64_t host_id() {
   char name[256] = {0};
@@ -199,6 +102,8 @@ static int alloc_rank(nbd_comm* c, size_t stage_bytes) {
   if (ao && ao[0] == '0') c->t_auto_off = 1;
   const char* am = getenv("NBDIST_B200_AUTO_MIN_BYTES");
   if (am) c->t_auto_min = strtoull(am, nullptr, 0);
+  const char* nr = getenv("NBDIST_B200_NVLS_REDUCE");
+  if (nr && nr[0] != '0') c->t_nvls_reduce = 1;
   return NBD_OK;
 }
 
@@ -243,6 +148,7 @@ static void free_rank(nbd_comm* c) {
       if (p != c->rank && c->peer_base[p]) cudaIpcCloseMemHandle(c->peer_base[p]);
   }
   hostpipe_free(c->hp);
+  nvls_teardown(c);
   for (auto& g : c->regs) {
     if (!c->emu)
       for (int p = 0; p < c->world; ++p)
@@ -317,6 +223,7 @@ int nbd_comm_create(nbd_comm_t* out, int rank, int world, int device, size_t sta
     fill_ctx(c);
     c->connected = true;
   }
+  nvls_prepare(c);  // rank 0 of a multi-rank group opens the multicast rendezvous socket
   *out = c;
   return NBD_OK;
 }
@@ -337,6 +244,7 @@ int nbd_comm_get_handle(nbd_comm_t c, void* handle_out) {
   h.stage_bytes = c->stage_bytes;
   NBD_CUDA(cudaDeviceGetPCIBusId(h.pci, sizeof(h.pci), c->device));
   NBD_CUDA(cudaIpcGetMemHandle(&h.ipc, c->arena));
+  h.nvls_nonce = c->nvls.nonce;
   memset(handle_out, 0, NBD_HANDLE_BYTES);
   memcpy(handle_out, &h, sizeof(h));
   return NBD_OK;
@@ -382,6 +290,12 @@ int nbd_comm_connect(nbd_comm_t c, const void* all_handles) {
     c->peer_base[p] = ptr;
   }
   fill_ctx(c);
+  {
+    // NVSwitch multicast staging (nbd_nvls.cu): collective among the ranks, never fatal
+    Handle h0;
+    memcpy(&h0, (const char*)all_handles, sizeof(h0));
+    nvls_setup(c, c->rank == 0 ? c->nvls.nonce : h0.nvls_nonce);
+  }
   c->connected = true;
   return NBD_OK;
 }
@@ -433,6 +347,11 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "ll_max_bytes")) return &c->t_ll_max;
   if (!strcmp(name, "auto_register_off")) return &c->t_auto_off;
   if (!strcmp(name, "auto_min_bytes")) return &c->t_auto_min;
+  if (!strcmp(name, "nvls_reduce")) return &c->t_nvls_reduce;
+  if (!strcmp(name, "nvls_off")) return &c->t_nvls_off;
+  if (!strcmp(name, "nvls_min_bytes")) return &c->t_nvls_min;
+  if (!strcmp(name, "pipe")) return &c->t_pipe;
+  if (!strcmp(name, "pipe_tile_bytes")) return &c->t_pipe_tile;
   return nullptr;
 }
 
@@ -682,6 +601,120 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
     c->last_algo = "bcast_scatter";
   }
   return p;
+}
+
+// Tile pipeline (nbd_pipe.cuh): G CTAs, each streaming `rounds` tiles of `tile` bytes through
+// kPipeDepth staging slots.  Tiles are 16..256 KiB: small enough that copy-in, reduction and
+// copy-out of neighbouring tiles overlap and a flag costs one tile of latency, large enough that
+// the TMA rings and the 448 reducing threads have work.  capacity = staging bytes per rank.
+static const u64 kPipeTileMin = 16ull << 10, kPipeTileMax = 256ull << 10;
+
+static int plan_pipe(nbd_comm* c, u64 bytes, u64 capacity, int emu_world, Plan* out) {
+  Plan p;
+  memset(&p, 0, sizeof(p));
+  u64 gmax = (u64)c->num_sms * kMinBlocksPerSM;
+  if (emu_world > 1) gmax /= (u64)emu_world;
+  if (c->t_blocks && c->t_blocks < gmax) gmax = c->t_blocks;
+  if (gmax > (u64)kPipeMaxBlocks) gmax = kPipeMaxBlocks;
+  if (gmax < 1) gmax = 1;
+  u64 G = ceil_div(bytes, kPipeTileMin);
+  if (G < 1) G = 1;
+  if (G > gmax) G = gmax;
+  u64 tile = c->t_pipe_tile ? c->t_pipe_tile : ceil_div(bytes, G * 4);
+  if (tile < kPipeTileMin && !c->t_pipe_tile) tile = kPipeTileMin;
+  if (tile > kPipeTileMax) tile = kPipeTileMax;
+  tile = ceil_div(tile, 128) * 128;
+  const u64 cap_tile = floor_to(capacity / (G * kPipeDepth), 128);
+  if (tile > cap_tile) tile = cap_tile;
+  if (tile < 128) return fail(NBD_ERR_INVALID_ARGUMENT, "staging of %llu bytes is too small for the tile pipeline (%llu CTAs)",
+                             (unsigned long long)capacity, (unsigned long long)G);
+  p.op.bytes = bytes;
+  p.op.chunk_bytes = tile;
+  p.op.nchunks = (u32)ceil_div(ceil_div(bytes, kUnit) * kUnit, G * tile);
+  p.op.world = c->world;
+  p.nblocks = (int)G;
+  *out = p;
+  return NBD_OK;
+}
+
+// The pipeline kernels need 64 KiB of dynamic shared memory (two TMA rings): opt in once per
+// device and kernel.
+static int pipe_launch(const void* fn, int device, int nblocks, int world, bool coop, cudaStream_t s, void* pk, OpParams* op) {
+  static std::mutex mu;
+  static std::set<std::pair<int, const void*>> prepared;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!prepared.count({device, fn})) {
+      NBD_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pipe_smem_bytes()));
+      prepared.insert({device, fn});
+    }
+  }
+  void* args[2] = {pk, (void*)op};
+  if (!coop) {
+    NBD_CUDA(cudaLaunchKernel(fn, dim3(nblocks, 1, 1), dim3(kThreads, 1, 1), args, pipe_smem_bytes(), s));
+  } else {
+    NBD_CUDA(cudaLaunchCooperativeKernel(fn, dim3(nblocks, world, 1), dim3(kThreads, 1, 1), args, pipe_smem_bytes(), s));
+  }
+  g_launches.fetch_add(1);
+  return NBD_OK;
+}
+
+// In-switch reduction is opt-in ("nvls_reduce" / NBDIST_B200_NVLS_REDUCE=1): the switch adds the N
+// copies in an order of its own, so float sums are not bit-identical with the ascending-rank
+// order of every other kernel (they stay within the tolerance of tests/helpers.py and are
+// identical on all ranks).  Broadcast over multicast is a plain copy and needs no opt-in.
+static const u64 kDefNvlsReduceMin = 1ull << 20;
+static const u64 kDefNvlsBcastMin = 512ull << 10;
+
+static bool nvls_reduce_wanted(const nbd_comm* c, u64 bytes, int dtype, int op) {
+  return c->nvls.enabled && !c->t_nvls_off && c->t_nvls_reduce && (op == NBD_SUM || op == NBD_AVG) &&
+         (dtype == NBD_F32 || dtype == NBD_BF16 || dtype == NBD_F16) &&
+         bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsReduceMin);
+}
+
+static bool nvls_bcast_wanted(const nbd_comm* c, u64 bytes) {
+  return c->nvls.enabled && !c->t_nvls_off && bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsBcastMin);
+}
+
+// P2P tile pipeline: only on request ("pipe" = 1) until measurements say where it wins
+static bool pipe_wanted(const nbd_comm* c, u64 bytes) { return c->t_pipe == 1 && bytes > kLLMaxBytes; }
+
+static void fill_pipe(PackPipe<1>& pk, nbd_comm* c, const void* send, void* recv, bool mc) {
+  memset(&pk, 0, sizeof(pk));
+  pk.ctx[0] = c->ctx;
+  pk.buf[0].send = (const char*)send;
+  pk.buf[0].recv = (char*)recv;
+  pk.pb[0].local = mc ? c->nvls.local : c->ctx.stage[c->rank];
+  pk.pb[0].mc = mc ? c->nvls.mcva : nullptr;
+}
+
+static int pipe_all_reduce(nbd_comm* c, const void* send, void* recv, u64 bytes, int dtype, int op, bool mc, cudaStream_t s) {
+  const bool sum = (op == NBD_SUM || op == NBD_AVG);
+  const void* fn = pipe_allreduce_kernel(dtype, sum, false, mc);
+  if (!fn) return fail(NBD_ERR_UNSUPPORTED, "dtype %d / op %d has no tile-pipeline kernel", dtype, op);
+  Plan p;
+  int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.bytes : 2 * c->ctx.half_bytes, 0, &p);
+  if (rc != NBD_OK) return rc;
+  p.op.op = op;
+  p.op.avg = (op == NBD_AVG);
+  p.op.algo = mc ? 0 : 1;  // arena staging is shared with the chunked kernels: open with a barrier
+  PackPipe<1> pk;
+  fill_pipe(pk, c, send, recv, mc);
+  c->last_algo = mc ? "ar_nvls" : "ar_pipe";
+  return pipe_launch(fn, c->device, p.nblocks, 1, false, s, &pk, &p.op);
+}
+
+static int pipe_broadcast(nbd_comm* c, void* buf, u64 bytes, int root, bool mc, cudaStream_t s) {
+  const void* fn = pipe_broadcast_kernel(false, mc);
+  Plan p;
+  int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.bytes : 2 * c->ctx.half_bytes, 0, &p);
+  if (rc != NBD_OK) return rc;
+  p.op.root = root;
+  p.op.algo = mc ? 0 : 1;
+  PackPipe<1> pk;
+  fill_pipe(pk, c, buf, buf, mc);
+  c->last_algo = mc ? "bcast_nvls" : "bcast_pipe";
+  return pipe_launch(fn, c->device, p.nblocks, 1, false, s, &pk, &p.op);
 }
 
 // ---------------------------------------------------------------------------
@@ -1009,6 +1042,8 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
                                  &prm);
     }
   }
+  if (nvls_reduce_wanted(c, bytes, dtype, op)) return pipe_all_reduce(c, send, recv, bytes, dtype, op, true, s);
+  if (pipe_wanted(c, bytes)) return pipe_all_reduce(c, send, recv, bytes, dtype, op, false, s);
   if (auto_wanted_ar(c, bytes)) {
     // ordinary tensors: agree on the device whether every rank can address every rank's
     // buffers; enqueue both kernels, the decision gates them (nbd_device.cuh)
@@ -1174,6 +1209,8 @@ int nbd_broadcast(nbd_comm_t c, void* buf, size_t count, int dtype, int root, vo
   }
   DeviceGuard g(c->device);
   cudaStream_t s = (cudaStream_t)stream;
+  if (nvls_bcast_wanted(c, (u64)count * es)) return pipe_broadcast(c, buf, (u64)count * es, root, true, s);
+  if (pipe_wanted(c, (u64)count * es)) return pipe_broadcast(c, buf, (u64)count * es, root, false, s);
   Plan p = plan_broadcast(c, (u64)count * es, root, 0);
   Pack<1> pk;
   fill_pack(pk, c, buf, buf);
@@ -1225,6 +1262,26 @@ int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* re
   cudaStream_t s = (cudaStream_t)stream;
   const u64 bytes = (u64)count * nbd_dtype_size(dtype);
   if (g->world == 1) return emu_local_copies(g, sends, recvs, bytes, s);
+  if (pipe_wanted(c0, bytes)) {  // the tile pipeline over the emulated arenas (P2P transport)
+    const void* fn = pipe_allreduce_kernel(dtype, op == NBD_SUM || op == NBD_AVG, true, false);
+    if (!fn) return fail(NBD_ERR_UNSUPPORTED, "dtype %d cannot be reduced", dtype);
+    Plan p;
+    if ((rc = plan_pipe(c0, bytes, 2 * c0->ctx.half_bytes, g->world, &p)) != NBD_OK) return rc;
+    p.op.op = op;
+    p.op.avg = (op == NBD_AVG);
+    p.op.algo = 1;
+    PackPipe<kMaxRanks> pk;
+    memset(&pk, 0, sizeof(pk));
+    for (int r = 0; r < g->world; ++r) {
+      if ((rc = check_usable(g->comms[r])) != NBD_OK) return rc;
+      pk.ctx[r] = g->comms[r]->ctx;
+      pk.buf[r].send = (const char*)sends[r];
+      pk.buf[r].recv = (char*)recvs[r];
+      pk.pb[r].local = g->comms[r]->ctx.stage[r];
+    }
+    set_algo(c0, "ar_pipe");
+    return pipe_launch(fn, c0->device, p.nblocks, g->world, true, s, &pk, &p.op);
+  }
   if (zc_wanted(c0, bytes)) {  // emulated ranks share one address space: always zero-copy capable
     PackZc<kMaxRanks> zk;
     if ((rc = fill_zc_emu(zk, g, sends, recvs)) != NBD_OK) return rc;
@@ -1308,6 +1365,24 @@ int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count, int dtype
   if (g->world == 1) return NBD_OK;
   nbd_comm* c0 = g->comms[0];
   DeviceGuard dg(c0->device);
+  if (pipe_wanted(c0, (u64)count * es)) {
+    Plan p;
+    if ((rc = plan_pipe(c0, (u64)count * es, 2 * c0->ctx.half_bytes, g->world, &p)) != NBD_OK) return rc;
+    p.op.root = root;
+    p.op.algo = 1;
+    PackPipe<kMaxRanks> pk;
+    memset(&pk, 0, sizeof(pk));
+    for (int r = 0; r < g->world; ++r) {
+      if ((rc = check_usable(g->comms[r])) != NBD_OK) return rc;
+      pk.ctx[r] = g->comms[r]->ctx;
+      pk.buf[r].send = (const char*)bufs[r];
+      pk.buf[r].recv = (char*)bufs[r];
+      pk.pb[r].local = g->comms[r]->ctx.stage[r];
+    }
+    set_algo(c0, "bcast_pipe");
+    return pipe_launch(pipe_broadcast_kernel(true, false), c0->device, p.nblocks, g->world, true, (cudaStream_t)stream, &pk,
+                       &p.op);
+  }
   Pack<kMaxRanks> pk;
   if ((rc = fill_pack_emu(pk, g, (const void* const*)bufs, bufs)) != NBD_OK) return rc;
   Plan p = plan_broadcast(c0, (u64)count * es, root, g->world);
@@ -1547,6 +1622,12 @@ extern "C" int nbd_mem_free(nbd_comm_t c, void* ptr) {
     return NBD_OK;
   }
   return fail(NBD_ERR_INVALID_ARGUMENT, "pointer was not returned by nbd_mem_alloc on this communicator");
+}
+
+extern "C" int nbd_comm_nvls_status(nbd_comm_t c, char* why, size_t why_bytes) {
+  if (!c) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (why && why_bytes) snprintf(why, why_bytes, "%s", c->nvls.why);
+  return c->nvls.enabled ? 1 : 0;
 }
 
 // 1 if the most recent auto-registered collective on `comm` ran zero-copy, 0 if it ran staged,

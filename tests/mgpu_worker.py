@@ -86,6 +86,88 @@ def body(rank: int, world: int, port: int) -> None:
         dist.all_reduce(t, op=dop)
         H.assert_same(_np(t, dtype), O.reduce_rank_order(x, dtype, op), dtype, f"all_reduce {op}")
 
+    # ---- NVSwitch multicast (csrc/nbd_nvls.cu, nbd_pipe.cuh) ---------------------------------
+    # set-up is all-or-nothing across ranks; broadcast over it is a plain copy (bit-exact);
+    # in-switch float sums are opt-in, agree with the rank-order oracle within the north_star
+    # tolerance, are identical on every rank, and exact where the sum is exact in any order
+    nv_on, nv_why = be.nvls_status()
+    flags = _gather_cpu(dist, torch, torch.tensor([int(nv_on)]))
+    assert all(int(f) == int(flags[0]) for f in flags), f"ranks disagree on multicast: {[int(f) for f in flags]}"
+    if rank == 0:
+        print(f"[mgpu_worker] multicast: {nv_on} ({nv_why})", flush=True)
+    if os.environ.get("NBD_TEST_REQUIRE_NVLS") == "1":
+        assert nv_on, f"multicast expected on this box: {nv_why}"
+    if nv_on:
+        be.set_tunable("nvls_min_bytes", 1)
+        for nbytes in (40, (48 << 10) + 5, (1 << 20) + 17, (9 << 20) + 1):
+            for root in sorted({0, world - 1}):
+                x = O.make_inputs(world, nbytes, "u8", seed=70 + root)
+                t = H.to_cuda(x[rank], "u8", dev)
+                dist.broadcast(t, src=root)
+                assert be.last_algo() == "bcast_nvls", be.last_algo()
+                H.assert_same(_np(t, "u8"), x[root], "u8", f"multicast broadcast {nbytes}B root {root}")
+        v = torch.zeros(70001 + 8, dtype=torch.uint8, device=dev)[3:3 + 70001]  # misaligned view
+        x = O.make_inputs(world, 70001, "u8", seed=75)
+        v.copy_(H.to_cuda(x[rank], "u8", dev))
+        dist.broadcast(v, src=1 % world)
+        H.assert_same(_np(v, "u8"), x[1 % world], "u8", "multicast broadcast into a misaligned view")
+        be.set_tunable("nvls_reduce", 1)
+        for dtype in ("f32", "bf16", "f16"):
+            for numel in (4099, (1 << 20) + 1, (5 << 20) + 3):
+                x = O.make_inputs(world, numel, dtype, seed=80)
+                t = H.to_cuda(x[rank], dtype, dev)
+                dist.all_reduce(t)
+                assert be.last_algo() == "ar_nvls", be.last_algo()
+                got = _np(t, dtype)
+                err = np.abs(O.to_f64(got, dtype) - O.to_f64(O.reduce_rank_order(x, dtype), dtype))
+                tol = O.float_sum_tolerance(x, dtype)
+                assert (err <= tol).all(), f"in-switch {dtype} sum n={numel}: max err/tol {np.max(err / tol)}"
+                chk = torch.from_numpy(got.view(np.uint8).astype(np.int64)).sum().reshape(1)
+                allchk = _gather_cpu(dist, torch, chk)
+                assert all(int(a) == int(allchk[0]) for a in allchk), f"in-switch {dtype} sum differs between ranks"
+        xi = [np.random.default_rng(90 + r).integers(-1000, 1000, (3 << 20) + 11).astype(np.float32) for r in range(world)]
+        t = H.to_cuda(xi[rank], "f32", dev)
+        dist.all_reduce(t)
+        H.assert_same(_np(t, "f32"), O.reduce_rank_order(xi, "f32"), "f32", "in-switch sum of integer-valued fp32 (exact in any order)")
+        x = O.make_inputs(world, (1 << 20) + 3, "f32", seed=81)
+        t = H.to_cuda(x[rank], "f32", dev)
+        dist.all_reduce(t, op=dist.ReduceOp.AVG)
+        assert be.last_algo() == "ar_nvls"
+        err = np.abs(_np(t, "f32").astype(np.float64) - O.to_f64(O.reduce_rank_order(x, "f32", "avg"), "f32"))
+        assert (err <= O.float_sum_tolerance(x, "f32") / world + 1e-12).all(), "in-switch AVG"
+        # what the switch cannot add keeps the rank-order kernels: bit-exact as ever
+        for dtype, dop, op in (("i32", dist.ReduceOp.SUM, "sum"), ("f32", dist.ReduceOp.MAX, "max"), ("f64", dist.ReduceOp.SUM, "sum")):
+            x = O.make_inputs(world, (1 << 19) + 7, dtype, seed=82)
+            t = H.to_cuda(x[rank], dtype, dev)
+            dist.all_reduce(t, op=dop)
+            assert be.last_algo() != "ar_nvls"
+            H.assert_same(_np(t, dtype), O.reduce_rank_order(x, dtype, op), dtype, f"{dtype} {op} with nvls_reduce on")
+        # a misaligned in-place view through the in-switch path
+        v = torch.zeros((1 << 18) + 9, dtype=torch.float32, device=dev)[1:1 + (1 << 18) + 5]
+        x = [np.random.default_rng(95 + r).integers(-99, 99, (1 << 18) + 5).astype(np.float32) for r in range(world)]
+        v.copy_(H.to_cuda(x[rank], "f32", dev))
+        dist.all_reduce(v)
+        H.assert_same(_np(v, "f32"), O.reduce_rank_order(x, "f32"), "f32", "in-switch sum on a storage_offset view")
+        be.set_tunable("nvls_reduce", 0)
+        be.set_tunable("nvls_min_bytes", 0)
+    # ---- the tile pipeline over peer-to-peer transport on real ranks: bit-exact ----------------
+    be.set_tunable("pipe", 1)
+    for dtype, numel in (("f32", (1 << 20) + 1), ("bf16", (3 << 20) + 5), ("i64", 70001), ("u8", (1 << 20) + 3)):
+        x = O.make_inputs(world, numel, dtype, seed=85)
+        t = H.to_cuda(x[rank], dtype, dev)
+        dist.all_reduce(t)
+        assert be.last_algo() == "ar_pipe", be.last_algo()
+        H.assert_same(_np(t, dtype), O.reduce_rank_order(x, dtype), dtype, f"pipe all_reduce {dtype} n={numel}")
+    be.set_tunable("nvls_off", 1)
+    for nbytes, root in (((48 << 10) + 5, 0), ((6 << 20) + 1, world - 1)):
+        x = O.make_inputs(world, nbytes, "u8", seed=86)
+        t = H.to_cuda(x[rank], "u8", dev)
+        dist.broadcast(t, src=root)
+        assert be.last_algo() == "bcast_pipe", be.last_algo()
+        H.assert_same(_np(t, "u8"), x[root], "u8", f"pipe broadcast {nbytes}B root {root}")
+    be.set_tunable("nvls_off", 0)
+    be.set_tunable("pipe", 0)
+
     # ---- broadcast: every root, latency and bandwidth paths, bit-exact -------------------
     for nbytes in (40, 400, 12 * 1024 + 3, (1 << 20) + 17, (40 << 20) + 1):
         for root in sorted({0, world - 1}):

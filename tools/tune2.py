@@ -1,0 +1,151 @@
+#!/usr/bin/env python
+"""Round-2 sweep (run under torch.distributed.run, one process per GPU): every all_reduce and
+broadcast path of the b200 backend on the same buffers, one JSON line per measurement on rank 0.
+
+  all_reduce : staged (chunked two-shot) | auto (auto-registered zero-copy) | pipe (tile pipeline,
+               peer-to-peer transport) | nvls (tile pipeline, in-switch reduction) | NCCL
+  broadcast  : staged (scatter) | pipe | nvls | NCCL
+
+Every variant is checked before it is timed: integer-valued fp32 inputs make the sum exact in
+any order, so all paths must return the same bits.  Numbers that justify defaults go to profiles/.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+
+    from nbdistributed_b200 import backend as B
+    from nbdistributed_b200 import worker_init as W
+
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    W.init_worker(rank, world, os.environ.get("MASTER_ADDR", "127.0.0.1"), os.environ.get("MASTER_PORT", "29500"),
+                  gpu_id=local, backend="b200")
+    dev = torch.device("cuda", local)
+    cpu = dist.new_group(backend="gloo")
+    be = B.get_backend()
+    quick = "--quick" in sys.argv
+    nccl = None if "--no-nccl" in sys.argv else dist.new_group(backend="nccl")
+
+    def emit(obj):
+        if rank == 0:
+            print(json.dumps(obj), flush=True)
+
+    warm = torch.zeros(1024, device=dev)
+    dist.all_reduce(warm)  # creates the communicator (and the multicast object)
+    torch.cuda.synchronize()
+    st = be.nvls_status()
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (bool(st[0]), st[1]), group=cpu)
+    emit({"kind": "nvls_status", "world": world, "per_rank": gathered})
+    have_nvls = all(g[0] for g in gathered)
+
+    def timed(fn, iters, warmup=2):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu)
+        t = torch.tensor([e0.elapsed_time(e1) * 1e3 / iters], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu)
+        return float(t.item())
+
+    class knobs:
+        def __init__(self, **kv):
+            self.kv = kv
+
+        def __enter__(self):
+            for k, v in self.kv.items():
+                be.set_tunable(k, v)
+
+        def __exit__(self, *exc):
+            for k in self.kv:
+                be.set_tunable(k, 0)
+
+    big = torch.empty((1 << 30) // 4, device=dev, dtype=torch.float32)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    sizes = [1 << 20, 4 << 20, 16 << 20, 64 << 20, 256 << 20] + ([] if quick else [1 << 30])
+    f_ar = 2.0 * (world - 1) / world
+
+    ar_variants = [("staged", {"auto_register_off": 1, "pipe": 2, "nvls_off": 1}),
+                   ("auto", {"auto_min_bytes": 1 << 20, "pipe": 2, "nvls_off": 1})]
+    for tile in (0, 64 << 10, 256 << 10):
+        ar_variants.append((f"pipe/tile={tile >> 10}K", {"pipe": 1, "pipe_tile_bytes": tile, "nvls_off": 1}))
+    if have_nvls:
+        for tile in (0, 32 << 10, 128 << 10, 256 << 10):
+            for blocks in (0, 64):
+                ar_variants.append((f"nvls/tile={tile >> 10}K/blocks={blocks}",
+                                    {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "blocks": blocks}))
+    for nbytes in sizes:
+        n = nbytes // 4
+        x = big[:n]
+        src = torch.randint(-1000, 1000, (n,), generator=g, device=dev, dtype=torch.int32)
+        want = src.clone()
+        dist.all_reduce(want)  # int32: exact on any path
+        want = want.to(torch.float32)
+        iters = 30 if nbytes <= (16 << 20) else (10 if nbytes <= (256 << 20) else 4)
+        for name, kv in ar_variants:
+            with knobs(**kv):
+                x.copy_(src)
+                dist.all_reduce(x)
+                if name == "auto":  # first touches export/import the allocation
+                    for _ in range(2):
+                        x.copy_(src)
+                        dist.all_reduce(x)
+                ok = bool(torch.equal(x, want))
+                algo = be.last_algo()
+                x.zero_()
+                us = timed(lambda: dist.all_reduce(x), iters)
+            emit({"op": "all_reduce", "variant": name, "bytes": nbytes, "us": round(us, 2),
+                  "busbw": round(nbytes * f_ar / us / 1e3, 1), "algo": algo, "ok": ok})
+        if nccl is not None:
+            x.zero_()
+            us = timed(lambda: dist.all_reduce(x, group=nccl), iters)
+            emit({"op": "all_reduce", "variant": "nccl", "bytes": nbytes, "us": round(us, 2),
+                  "busbw": round(nbytes * f_ar / us / 1e3, 1)})
+        del src, want
+
+    bc_variants = [("staged", {"pipe": 2, "nvls_off": 1}), ("pipe", {"pipe": 1, "nvls_off": 1})]
+    if have_nvls:
+        for tile in (0, 64 << 10, 256 << 10):
+            bc_variants.append((f"nvls/tile={tile >> 10}K", {"nvls_min_bytes": 1, "pipe_tile_bytes": tile}))
+    for nbytes in sizes:
+        n = nbytes // 4
+        x = big[:n]
+        iters = 30 if nbytes <= (16 << 20) else (10 if nbytes <= (256 << 20) else 4)
+        for name, kv in bc_variants:
+            with knobs(**kv):
+                root = world - 1
+                x.fill_(float(rank + 1))
+                dist.broadcast(x, src=root)
+                ok = bool((x == float(root + 1)).all())
+                algo = be.last_algo()
+                us = timed(lambda: dist.broadcast(x, src=0), iters)
+            emit({"op": "broadcast", "variant": name, "bytes": nbytes, "us": round(us, 2),
+                  "busbw": round(nbytes / us / 1e3, 1), "algo": algo, "ok": ok})
+        if nccl is not None:
+            us = timed(lambda: dist.broadcast(x, src=0, group=nccl), iters)
+            emit({"op": "broadcast", "variant": "nccl", "bytes": nbytes, "us": round(us, 2), "busbw": round(nbytes / us / 1e3, 1)})
+    dist.barrier(group=cpu)
+    del big
+    W.shutdown_worker()
+
+
+if __name__ == "__main__":
+    main()

@@ -41,6 +41,14 @@ UNIT = "GB/s"
 MSG_BYTES = 256 << 20          # per-rank message of the headline step
 EMU_RANKS = 8                  # ranks emulated on one GPU at N = 1
 NVLINK_PEAK_GBS = 900.0        # per direction per GPU, nominal (BASELINE.json north_star)
+KERNEL_OF_ALGO = {  # last_algo() of the timed step -> the kernel that ran (real ranks, fp32 SUM)
+    "ar_nvls": "nbd::k_allreduce_pipe<float,true,1,true> (multimem.ld_reduce / multimem.st)",
+    "ar_pipe": "nbd::k_allreduce_pipe<float,true,1,false>",
+    "ar_auto": "nbd::k_zc_agree + nbd::k_allreduce_zc<float,true,1> (staged launch gated out on the device)",
+    "ar_zerocopy": "nbd::k_allreduce_zc<float,true,1>",
+    "ar_twoshot": "nbd::k_allreduce_twoshot<float,true,1>",
+    "ar_oneshot": "nbd::k_allreduce_oneshot<float,true,1>",
+}
 HBM_FALLBACK_GBS = 6650.0      # /opt/skills/guides/B200_PROFILING.md fallback
 
 
@@ -137,6 +145,26 @@ def physical_gpu_index(local_index: int) -> int:
         except Exception:
             return local_index
     return local_index
+
+
+def nvlink_bytes(device_index: int):
+    """Cumulative NVLink payload bytes (tx, rx) of one GPU, all links, from NVML's throughput
+    counters (KiB granularity); None where the driver does not expose them."""
+    try:
+        import pynvml as nv
+
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(device_index)
+        vals = nv.nvmlDeviceGetFieldValues(h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
+                                               (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                return None
+            out.append(int(v.value.ullVal) * 1024)
+        return tuple(out)
+    except Exception:
+        return None
 
 
 # --------------------------------------------------------------------------------------
@@ -514,32 +542,62 @@ def run_ours_multi(args):
         dist.all_reduce(x)
 
     W0 = max(args.warmup, 3)
+    # parity first: every kernel family at this world size, bit for bit (see parity_check)
+    log("parity check")
+    pc = parity_check(torch, dist, dev, rank, world, cpu_group, be, B)
+    if pc["failed_any_rank"]:
+        print(f"[bench] rank {rank}: PARITY FAILURE {pc}", file=sys.stderr, flush=True)
+        dist.barrier(group=cpu_group)
+        raise SystemExit(f"bench.py: parity check failed on {pc['failed_any_rank']} case(s); nothing was timed")
+    # in-switch reduction (NVSwitch multicast) is an opt-in of the backend; the headline uses it
+    # where the box has it and says so (config.workload, parity_check.notes)
+    nvls_on = bool(be.nvls_status()[0]) and os.environ.get("NBD_BENCH_NVLS", "1") != "0"
+    if nvls_on:
+        be.set_tunable("nvls_reduce", 1)
     for _ in range(W0):
         step()
     torch.cuda.synchronize()
     algo = be.last_algo()
-    # correctness of the timed op: one fresh all_reduce against gloo on the same inputs
+    # correctness of the timed op itself: one fresh all_reduce against a rank-order re-reduction of
+    # the same seeded inputs - bit for bit on the peer-to-peer paths, 1e-6 * sum|x| in-switch
     x.copy_(src)
     dist.all_reduce(x)
-    ref = src.cpu()
-    dist.all_reduce(ref, group=cpu_group)
-    tol = 1e-6 * world * float(src.abs().max()) + 1e-12
-    if not torch.allclose(x.cpu(), ref, rtol=0, atol=tol * 8):
-        raise SystemExit("bench.py: b200 all_reduce differs from gloo beyond the fp32 tolerance")
+    want = None
+    mag = None
+    for r in range(world):
+        gr = torch.Generator(device=dev)
+        gr.manual_seed(1234 + r)
+        xr = torch.randn(numel, generator=gr, device=dev, dtype=torch.float32) * 0.01
+        want = xr if want is None else want + xr
+        mag = xr.abs() if mag is None else mag + xr.abs()
+        del xr
+    if algo == "ar_nvls":
+        ok = bool(((x.double() - want.double()).abs() <= 1e-6 * mag.double() + 1e-30).all())
+    else:
+        ok = torch.equal(x.view(torch.int32), want.view(torch.int32))
+    del want, mag
+    if not ok:
+        raise SystemExit(f"bench.py: the timed all_reduce ({algo}) does not match a rank-order fp32 re-reduction")
     x.copy_(src)
 
     sampler = ClockSampler(physical_gpu_index(local)).start() if rank == 0 else None
     l0 = B.launch_count()
     torch.cuda.synchronize()
     dist.barrier(group=cpu_group)
+    nvl0 = nvlink_bytes(physical_gpu_index(local)) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
     torch.cuda.synchronize()
+    nvl1 = nvlink_bytes(physical_gpu_index(local)) if rank == 0 else None
     dist.barrier(group=cpu_group)
     launches = B.launch_count() - l0
+    nvlink = None
+    if nvl0 and nvl1:
+        nvlink = {"tx_bytes_per_step": (nvl1[0] - nvl0[0]) / args.steps, "rx_bytes_per_step": (nvl1[1] - nvl0[1]) / args.steps,
+                  "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX of rank 0's GPU, all links, over the timed region / steps"}
     clocks = sampler.stop() if sampler else None
     t = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
@@ -559,9 +617,23 @@ def run_ours_multi(args):
     e2e_per_rank = S * bus_factor(world) / (e2e_ms * 1e-3) / 1e9
 
     extras = {}
+    if nvls_on:
+        # the same step on the exact (ascending-rank) peer-to-peer path, for comparison
+        be.set_tunable("nvls_reduce", 0)
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        ms_p2p = _time_collective(torch, dist, step, max(3, args.steps // 2), 2, cpu_group)
+        extras["p2p_exact_order"] = {"ms_per_step": round(ms_p2p, 4), "algo": be.last_algo(),
+                                     "busbw_per_rank": round(S * bus_factor(world) / (ms_p2p * 1e-3) / 1e9, 2)}
     if not args.no_sweep:
         log("message-size sweep")
         extras["sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be)
+        if nvls_on:
+            log("in-switch reduction sweep")
+            be.set_tunable("nvls_reduce", 1)
+            extras["nvls_sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be, only_all_reduce=True)
+            be.set_tunable("nvls_reduce", 0)
         log("device-side small-message latency")
         extras["latency"] = kernel_latency(torch, dist, dev, world, cpu_group, be)
         log("registered-memory sweep")
@@ -578,7 +650,9 @@ def run_ours_multi(args):
             "warmup": W0, "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "busbw_per_rank": round(per_rank, 2),
             "config": {"workload": f"all_reduce fp32 SUM, {S >> 20} MiB per rank, {world} ranks (one process per GPU) "
-                                   f"through dist.all_reduce on backend '{ns['__backend__']}', in place, algo={algo}",
+                                   f"through dist.all_reduce on backend '{ns['__backend__']}', in place, algo={algo}"
+                                   + (" (in-switch reduction: backend tunable nvls_reduce=1, an opt-in because the NVSwitch sums in "
+                                      "its own order; checked within 1e-6*sum|x| of the rank-order result)" if algo == "ar_nvls" else ""),
                        "ranks": world, "message_bytes": S, "l2": "message (256 MiB) larger than L2",
                        "value_definition": "sum over ranks of S*2(N-1)/N bytes per second"},
             "clocks": clocks,
@@ -587,12 +661,17 @@ def run_ours_multi(args):
                     "api": "nbdistributed_b200.backend.all_reduce_host (BackendB200 -> nbd_all_reduce_host): pinned host "
                            "buffers in and out, chunked H2D/collective/D2H pipeline inside the call"},
             "gpu_launches": int(launches),
+            "parity_check": pc,
             "roofline": {"bound": "nvlink", "achieved": round(per_rank, 1), "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
-                         "frac": round(per_rank / NVLINK_PEAK_GBS, 4), "traffic": None,
+                         "frac": round(per_rank / NVLINK_PEAK_GBS, 4),
+                         "traffic": (nvlink["tx_bytes_per_step"] + nvlink["rx_bytes_per_step"]) if nvlink else None,
+                         "nvlink": nvlink,
+                         "traffic_note": "NVLink payload bytes per launch, tx + rx of one GPU (not DRAM: ncu must not wrap a "
+                                         "multi-rank run); algorithmic_bytes_per_launch counts ONE direction",
                          "peak_source": "nominal NVLink 5 per direction per GPU (BASELINE.json); measured peer copy on this "
                                         "pool: 770 GB/s (B200_PROFILING.md)",
                          "algorithmic_bytes_per_launch": S * bus_factor(world),
-                         "kernel": "nbd::k_allreduce_oneshot/twoshot<float,true,1>"},
+                         "kernel": KERNEL_OF_ALGO.get(algo, algo)},
         }
         line.update(extras)
     dist.barrier(group=cpu_group)
@@ -629,23 +708,26 @@ def registered_sweep(torch, dist, dev, world, cpu_group, be):
     return out
 
 
-def multi_sweep(torch, dist, dev, world, cpu_group, be):
+def multi_sweep(torch, dist, dev, world, cpu_group, be, only_all_reduce=False):
     out = []
-    # ZeRO-style pair on ordinary tensors (BASELINE config 5, scaled to 1 GiB total)
-    flat = torch.full(((1 << 30) // 2,), 0.01, device=dev, dtype=torch.bfloat16)
-    shard = torch.empty(flat.numel() // world, dtype=torch.bfloat16, device=dev)
-    for name, fn in (("reduce_scatter", lambda: dist.reduce_scatter_tensor(shard, flat)),
-                     ("all_gather", lambda: dist.all_gather_into_tensor(flat, shard))):
-        for _ in range(3):  # first touches export/import the allocations (auto-registration)
-            fn()
-            torch.cuda.synchronize()
-        ms = _time_collective(torch, dist, fn, 5, 2, cpu_group)
-        out.append({"op": name, "dtype": "bfloat16", "bytes": 1 << 30, "us": round(ms * 1e3, 2),
-                    "busbw_per_rank": round((1 << 30) * (world - 1) / world / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
-    del flat, shard
-    for kind in ("all_reduce", "broadcast"):
+    if not only_all_reduce:
+        # ZeRO-style pair on ordinary tensors (BASELINE config 5, scaled to 1 GiB total)
+        flat = torch.full(((1 << 30) // 2,), 0.01, device=dev, dtype=torch.bfloat16)
+        shard = torch.empty(flat.numel() // world, dtype=torch.bfloat16, device=dev)
+        for name, fn in (("reduce_scatter", lambda: dist.reduce_scatter_tensor(shard, flat)),
+                         ("all_gather", lambda: dist.all_gather_into_tensor(flat, shard))):
+            for _ in range(3):  # first touches export/import the allocations (auto-registration)
+                fn()
+                torch.cuda.synchronize()
+            ms = _time_collective(torch, dist, fn, 5, 2, cpu_group)
+            out.append({"op": name, "dtype": "bfloat16", "bytes": 1 << 30, "us": round(ms * 1e3, 2),
+                        "busbw_per_rank": round((1 << 30) * (world - 1) / world / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
+        del flat, shard
+    for kind in (("all_reduce",) if only_all_reduce else ("all_reduce", "broadcast")):
         for dt, es in ((torch.float32, 4), (torch.bfloat16, 2)):
             for nbytes in (4 << 10, 64 << 10, 1 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30):
+                if only_all_reduce and nbytes < (1 << 20):
+                    continue
                 if dt == torch.bfloat16 and nbytes not in (4 << 10, 1 << 20, 64 << 20, 1 << 30):
                     continue
                 buf = torch.ones(nbytes // es, device=dev, dtype=dt)

@@ -201,6 +201,16 @@ class EmuGroup:
     def last_algo(self) -> str:
         return self.lib.nbd_last_algo(self._h).decode()
 
+    def set_timeout_ms(self, ms: int) -> None:
+        """Flag-wait watchdog of every rank (nbd_comm_set_timeout_ms)."""
+        for c in self.comms:
+            check(self.lib.nbd_comm_set_timeout_ms(c, ms))
+
+    def abort(self) -> None:
+        """nbd_comm_abort on every rank: running kernels leave their flag waits."""
+        for c in self.comms:
+            check(self.lib.nbd_comm_abort(c))
+
     def async_error(self) -> None:
         for c in self.comms:
             check(self.lib.nbd_comm_async_error(c))

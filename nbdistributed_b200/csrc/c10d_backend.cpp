@@ -144,7 +144,24 @@ class WorkB200 : public c10d::Work {
     }
   }
 
-  bool wait(std::chrono::milliseconds /*timeout*/ = kNoTimeout) override {
+  // wait() without a timeout is a stream wait (what cell code gets after a synchronous call).
+  // With a timeout it blocks the HOST until the work's event fires or the deadline passes; on
+  // expiry the communicator is aborted (in-flight kernels leave their flag waits) and the call
+  // throws, instead of the reference's hang-forever (ref:src/nbdistributed/communication.py:263-269).
+  bool wait(std::chrono::milliseconds timeout = kNoTimeout) override {
+    if (timeout != kNoTimeout && timeout.count() > 0) {
+      const auto deadline = std::chrono::steady_clock::now() + timeout;
+      while (!done_.query()) {
+        if (std::chrono::steady_clock::now() >= deadline) {
+          nbd_comm_abort(comm_);
+          C10_THROW_ERROR(DistBackendError, c10::str("[", kBackendName, "] wait(timeout=", timeout.count(),
+                                                     " ms) expired; the communicator was aborted"));
+        }
+        std::this_thread::sleep_for(std::chrono::microseconds(50));
+      }
+      const int rc = nbd_comm_async_error(comm_);
+      if (rc != NBD_OK) throw_nbd(rc, "wait");
+    }
     synchronize();
     return true;
   }

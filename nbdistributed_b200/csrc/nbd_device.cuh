@@ -35,7 +35,7 @@ struct LocalState {
   u64 epoch;      // flag-barrier epochs consumed by completed launches
   u64 chunk_seq;  // staging steps consumed; parity picks the staging half
   u32 done;       // CTAs of the running launch that have finished
-  u32 pad;
+  u32 failed;     // set (never cleared) when a flag wait of this rank gave up: later waits drain
   u64 ll_seq;     // LL (flag-in-data) operations completed; parity picks the LL buffer
 };
 
@@ -192,16 +192,15 @@ __device__ __forceinline__ u64 globaltimer_ns() {
 
 // Spin until *f >= epoch (flags only ever grow).  Gives up on abort/timeout and
 // records why in the host mailbox; the communicator is dead after that.
-static __device__ __noinline__ void wait_flag_slow(HostMailbox* mbox, u64 timeout_ns, const u64* f,
-                                            u64 epoch) {
+static __device__ __noinline__ void wait_flag_slow(LocalState* st, HostMailbox* mbox, u64 timeout_ns, const u64* f,
+                                                   u64 epoch) {
   u64 t0 = 0;
   u32 spins = 0;
-  {
-    // a launch that already gave up once (timeout/abort) must drain, not wait a full timeout at
-    // every later flag: its results are void anyway and the communicator is dead
-    volatile HostMailbox* mb = mbox;
-    if (mb->error != 0) return;
-  }
+  // A launch that already gave up once (timeout/abort) must drain, not wait a full timeout at
+  // every later flag: its results are void anyway and the communicator is dead.  The marker is
+  // device memory on purpose: the mailbox is pinned HOST memory, and reading it on every entry
+  // from hundreds of CTAs cost ~75 us per flag (PCIe reads serialise; measured on 2xB200).
+  if (reinterpret_cast<volatile LocalState*>(st)->failed != 0) return;
   while (ld_relaxed_sys(f) < epoch) {
     if ((++spins & 0x3FFFu) == 0) {
       const u64 now = globaltimer_ns();
@@ -209,19 +208,22 @@ static __device__ __noinline__ void wait_flag_slow(HostMailbox* mbox, u64 timeou
       volatile HostMailbox* mb = mbox;
       if (mb->abort) {
         mb->error = 5;  // -NBD_ERR_ABORTED
+        reinterpret_cast<volatile LocalState*>(st)->failed = 1;
         break;
       }
       if (timeout_ns != 0 && now - t0 > timeout_ns) {
         mb->error = 4;  // -NBD_ERR_TIMEOUT
+        reinterpret_cast<volatile LocalState*>(st)->failed = 1;
         break;
       }
+      if (reinterpret_cast<volatile LocalState*>(st)->failed != 0) break;  // another thread of this rank gave up
     }
   }
 }
 
 __device__ __forceinline__ void wait_flag(const RankCtx& c, const u64* f,
                                           u64 epoch) {
-  if (ld_relaxed_sys(f) < epoch) wait_flag_slow(c.mbox, c.timeout_ns, f, epoch);
+  if (ld_relaxed_sys(f) < epoch) wait_flag_slow(c.state, c.mbox, c.timeout_ns, f, epoch);
   fence_acq_rel_sys();  // relaxed load + fence = acquire; also drops stale L1 lines
 }
 

@@ -241,8 +241,10 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
               const u64 now = globaltimer_ns();
               if (t0 == 0) t0 = now;
               volatile HostMailbox* mb = c.mbox;
-              if (mb->abort) { mb->error = 5; break; }
-              if (c.timeout_ns != 0 && now - t0 > c.timeout_ns) { mb->error = 4; break; }
+              volatile LocalState* ls = c.state;
+              if (mb->abort) { mb->error = 5; ls->failed = 1; break; }
+              if (c.timeout_ns != 0 && now - t0 > c.timeout_ns) { mb->error = 4; ls->failed = 1; break; }
+              if (ls->failed != 0) break;
             }
           }
           v[k] = make_uint4(a.x, a.z, b.x, b.z);

@@ -352,6 +352,7 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "nvls_min_bytes")) return &c->t_nvls_min;
   if (!strcmp(name, "pipe")) return &c->t_pipe;
   if (!strcmp(name, "pipe_tile_bytes")) return &c->t_pipe_tile;
+  if (!strcmp(name, "debug_mute_rank")) return &c->t_debug_mute;
   return nullptr;
 }
 
@@ -760,6 +761,17 @@ static int check_reduce_args(int dtype, int op) {
   return NBD_OK;
 }
 
+// Fault injection for the watchdog tests ("debug_mute_rank" = rank + 1 on an emulated group): the
+// muted rank's signals are redirected into its own LL area, so its peers never see it arrive and
+// run into the flag-wait watchdog, exactly as if that rank's process had died.
+static void mute_rank(const EmuGroup* g, RankCtx* ctx) {
+  const uint64_t m = g->comms[0]->t_debug_mute;
+  if (m == 0 || m > (uint64_t)g->world) return;
+  RankCtx& x = ctx[m - 1];
+  for (int p = 0; p < g->world; ++p)
+    if (p != x.rank) x.flags[p] = reinterpret_cast<u64*>(x.stage[x.rank] + x.ll_off);
+}
+
 // Fills pk for a real rank (NCTX == 1) or every emulated rank.
 static void fill_pack(Pack<1>& pk, nbd_comm* c, const void* send, void* recv) {
   pk.ctx[0] = c->ctx;
@@ -776,6 +788,7 @@ static int fill_pack_emu(Pack<kMaxRanks>& pk, EmuGroup* g, const void* const* se
     pk.buf[r].send = sends ? (const char*)sends[r] : nullptr;
     pk.buf[r].recv = recvs ? (char*)recvs[r] : nullptr;
   }
+  mute_rank(g, pk.ctx);
   return NBD_OK;
 }
 
@@ -852,6 +865,7 @@ static int fill_zc_emu(PackZc<kMaxRanks>& pk, EmuGroup* g, const void* const* se
     pk.z.send[r] = (const char*)sends[r];
     pk.z.recv[r] = (char*)recvs[r];
   }
+  mute_rank(g, pk.ctx);
   return NBD_OK;
 }
 
@@ -1279,6 +1293,7 @@ int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* re
       pk.buf[r].recv = (char*)recvs[r];
       pk.pb[r].local = g->comms[r]->ctx.stage[r];
     }
+    mute_rank(g, pk.ctx);
     set_algo(c0, "ar_pipe");
     return pipe_launch(fn, c0->device, p.nblocks, g->world, true, s, &pk, &p.op);
   }
@@ -1379,6 +1394,7 @@ int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count, int dtype
       pk.buf[r].recv = (char*)bufs[r];
       pk.pb[r].local = g->comms[r]->ctx.stage[r];
     }
+    mute_rank(g, pk.ctx);
     set_algo(c0, "bcast_pipe");
     return pipe_launch(pipe_broadcast_kernel(true, false), c0->device, p.nblocks, g->world, true, (cudaStream_t)stream, &pk,
                        &p.op);

@@ -276,6 +276,9 @@ bool step_alloc(nbd_comm* c, Local* L) {
   ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
   ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   ap.location.id = c->device;
+  // "externally shareable as well as imported multicast objects can be bound only to externally
+  // shareable memory" (cuMulticastBindMem): the staging is never exported, but must be exportable
+  ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
   CUmemGenericAllocationHandle mem = 0;
   r = d.MemCreate(&mem, s.bytes, &ap, 0);
   if (r != CUDA_SUCCESS) return why(c, "cuMemCreate(%zu bytes): %s", s.bytes, cu_str(r)), false;

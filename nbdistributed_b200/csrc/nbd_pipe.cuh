@@ -242,6 +242,36 @@ __device__ __forceinline__ void warp_tile_copy(TmaRing& R, const Region& user, u
   }
 }
 
+// reduce_loop_u of nbd_kernels.cuh for the reducing warps only (thread rt of kPipeRedThreads)
+template <typename T, bool SUM, int U, typename Src, typename Dst>
+__device__ __forceinline__ void pipe_reduce_loop(int N, u64 lo, u64 hi, int rt, int op, int avg, Src src, Dst dst) {
+  constexpr int KMAX = kMaxRanks / U;
+  for (u64 base = lo + rt; base < hi; base += (u64)U * kPipeRedThreads) {
+    uint4 v[U][KMAX];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kPipeRedThreads;
+      if (i < hi) {
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k)
+          if (k < N) v[j][k] = src(k, i);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 i = base + (u64)j * kPipeRedThreads;
+      if (i < hi) {
+        Reducer<T> R;
+        R.init(v[j][0]);
+#pragma unroll
+        for (int k = 1; k < KMAX; ++k)
+          if (k < N) R.template add<SUM>(v[j][k], op);
+        dst(i, R.result(avg, N));
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // all_reduce through the tile pipeline.  op.chunk_bytes = tile bytes (multiple of 16),
 // op.nchunks = rounds.  Grid <= kPipeMaxBlocks; every CTA of every rank must be co-resident.
@@ -342,18 +372,10 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
         }
       } else {
         // peer-to-peer transport: ascending-rank reduction of the N staged copies, result
-        // written into every rank's slot (own first, then rotated)
-        for (u64 u = lo + rt; u < hi; u += kPipeRedThreads) {
-          uint4 v[kMaxRanks];
-#pragma unroll
-          for (int k = 0; k < kMaxRanks; ++k)
-            if (k < N) v[k] = ld16((k == r ? pb.local : c.stage[k]) + soff + u * kUnit);
-          Reducer<T> Rd;
-          Rd.init(v[0]);
-#pragma unroll
-          for (int k = 1; k < kMaxRanks; ++k)
-            if (k < N) Rd.template add<SUM>(v[k], op.op);
-          const uint4 out = Rd.result(op.avg, N);
+        // written into every rank's slot (own first, then rotated); few ranks -> deeper unroll
+        // (remote loads need the bytes in flight)
+        auto src = [&](int k, u64 u) { return ld16((k == r ? pb.local : c.stage[k]) + soff + u * kUnit); };
+        auto dst = [&](u64 u, const uint4& out) {
 #pragma unroll
           for (int k = 0; k < kMaxRanks; ++k) {
             if (k < N) {
@@ -362,7 +384,10 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
               st16((p == r ? pb.local : c.stage[p]) + soff + u * kUnit, out);
             }
           }
-        }
+        };
+        if (N <= 2) pipe_reduce_loop<T, SUM, 4>(N, lo, hi, rt, op.op, op.avg, src, dst);
+        else if (N <= 4) pipe_reduce_loop<T, SUM, 2>(N, lo, hi, rt, op.op, op.avg, src, dst);
+        else pipe_reduce_loop<T, SUM, 1>(N, lo, hi, rt, op.op, op.avg, src, dst);
       }
       named_bar_sync(1, kPipeRedThreads);
       if (rt < N) st_release_sys(c.flags[rt] + rowB + r, E + 1 + i);

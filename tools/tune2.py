@@ -85,11 +85,11 @@ def main():
 
     ar_variants = [("staged", {"auto_register_off": 1, "pipe": 2, "nvls_off": 1}),
                    ("auto", {"auto_min_bytes": 1 << 20, "pipe": 2, "nvls_off": 1})]
-    for tile in (0, 64 << 10, 256 << 10):
+    for tile in (0,):
         ar_variants.append((f"pipe/tile={tile >> 10}K", {"pipe": 1, "pipe_tile_bytes": tile, "nvls_off": 1}))
     if have_nvls:
-        for tile in (0, 32 << 10, 128 << 10, 256 << 10):
-            for blocks in (0, 64):
+        for tile in (0, 128 << 10):
+            for blocks in (0, 96):
                 ar_variants.append((f"nvls/tile={tile >> 10}K/blocks={blocks}",
                                     {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "blocks": blocks}))
     for nbytes in sizes:
@@ -121,9 +121,37 @@ def main():
                   "busbw": round(nbytes * f_ar / us / 1e3, 1)})
         del src, want
 
+    # does the content of the buffers matter?  (constant buffers are what most sweeps time)
+    nbytes = 256 << 20
+    x = big[: nbytes // 4]
+    dvariants = [("auto", {"auto_min_bytes": 1 << 20, "pipe": 2, "nvls_off": 1})]
+    if have_nvls:
+        dvariants.append(("nvls", {"nvls_reduce": 1, "nvls_min_bytes": 1}))
+    for data in ("zeros", "ones", "randn"):
+        def fill():
+            if data == "zeros":
+                x.zero_()
+            elif data == "ones":
+                x.fill_(1.0)
+            else:
+                x.normal_(generator=g)
+                x.mul_(1e-30)  # in-place sums grow by world per iteration: stay finite
+        for name, kv in dvariants:
+            with knobs(**kv):
+                fill()
+                us = timed(lambda: dist.all_reduce(x), 10)
+                algo = be.last_algo()
+            emit({"op": "all_reduce", "variant": f"{name}/data={data}", "bytes": nbytes, "us": round(us, 2),
+                  "busbw": round(nbytes * f_ar / us / 1e3, 1), "algo": algo})
+        if nccl is not None:
+            fill()
+            us = timed(lambda: dist.all_reduce(x, group=nccl), 10)
+            emit({"op": "all_reduce", "variant": f"nccl/data={data}", "bytes": nbytes, "us": round(us, 2),
+                  "busbw": round(nbytes * f_ar / us / 1e3, 1)})
+
     bc_variants = [("staged", {"pipe": 2, "nvls_off": 1}), ("pipe", {"pipe": 1, "nvls_off": 1})]
     if have_nvls:
-        for tile in (0, 64 << 10, 256 << 10):
+        for tile in (0,):
             bc_variants.append((f"nvls/tile={tile >> 10}K", {"nvls_min_bytes": 1, "pipe_tile_bytes": tile}))
     for nbytes in sizes:
         n = nbytes // 4

@@ -461,9 +461,11 @@ def parity_check(torch, dist, dev, rank, world, cpu_group, be, B):
     # broadcast: direct, scatter / multicast; first and last root
     for n in (400, (1 << 20) + 17, (40 << 20) + 1):
         for root in sorted({0, world - 1}):
+            be.set_tunable("nvls_bcast", 1 if (root == 0 and n > 400) else 0)  # multimem.st path where multicast is on
             y = _seeded(torch, dev, rank, n, torch.uint8, 4600 + root)
             dist.broadcast(y, src=root)
             check(f"broadcast {n}B root {root}", torch.equal(y, _seeded(torch, dev, root, n, torch.uint8, 4600 + root)))
+    be.set_tunable("nvls_bcast", 0)
     # all_gather / reduce_scatter (tensor forms)
     n = (1 << 20) + 8
     x = _seeded(torch, dev, rank, n, torch.bfloat16, 4700)

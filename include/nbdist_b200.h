@@ -219,6 +219,46 @@ int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends,
                            int op, void* stream);
 int nbd_emu_barrier(nbd_comm_t any, void* stream);
 
+/* ---- many small broadcasts at once -------------------------------------------------
+ * The reference's broadcast idiom is one dist.broadcast per parameter (ref:README.md:122-123);
+ * issued inside a c10d coalescing block (Backend::startCoalescing / endCoalescing,
+ * $TORCH/.../Backend.hpp:109-123) the small ones arrive here as ONE call: every rank packs the
+ * items it is root of into its peers' staging, one flag barrier, every rank unpacks the rest.
+ * Every rank passes the same list of (bytes, root) in the same order; items may have different
+ * roots; an item too large to share a table runs as an ordinary nbd_broadcast. */
+typedef struct {
+  void* buf; /* device pointer: read on the root, written elsewhere */
+  size_t bytes;
+  int root;
+} nbd_bcast_item;
+int nbd_broadcast_table(nbd_comm_t comm, const nbd_bcast_item* items, int nitems, void* stream);
+/* Emulated ranks: items[r] = rank r's list (same bytes/root per index, its own buffers). */
+int nbd_emu_broadcast_table(nbd_comm_t any, const nbd_bcast_item* const* items, int nitems, void* stream);
+
+/* ---- point to point -------------------------------------------------------------
+ * dist.send / dist.recv / dist.batch_isend_irecv ($TORCH/distributed/distributed_c10d.py ->
+ * Backend::send / recv, Backend.hpp:355,364) and the primitive under all_to_all, gather and
+ * scatter (Backend.hpp:299-353): calls cell code can make on the process group of
+ * ref:src/nbdistributed/worker.py:151.  One call takes a BATCH of this rank's sends and
+ * receives and runs them concurrently in one launch (per peer and direction in issue order),
+ * so matching batches on two ranks never deadlock on their relative order.  The matching call
+ * on the peer must post the same message sizes in the same per-pair order.  Messages travel
+ * through the receiver's arena (1 MiB chunks, 4 in flight per ordered pair); bytes == 0 is a
+ * no-op on both sides; peer must differ from this rank (copy locally instead). */
+#define NBD_P2P_SEND 0
+#define NBD_P2P_RECV 1
+typedef struct {
+  int kind; /* NBD_P2P_SEND | NBD_P2P_RECV */
+  int peer;
+  void* buf; /* device pointer: read for a send, written for a receive */
+  size_t bytes;
+} nbd_p2p_op;
+int nbd_p2p_batch(nbd_comm_t comm, const nbd_p2p_op* ops, int nops, void* stream);
+int nbd_send(nbd_comm_t comm, const void* buf, size_t bytes, int peer, void* stream);
+int nbd_recv(nbd_comm_t comm, void* buf, size_t bytes, int peer, void* stream);
+/* Emulated ranks: ops[r] / nops[r] = rank r's batch; all ranks run in one cooperative launch. */
+int nbd_emu_p2p_batch(nbd_comm_t any, const nbd_p2p_op* const* ops, const int* nops, void* stream);
+
 /* ---- host buffers -------------------------------------------------------------
  * all_reduce of data that lives in HOST memory (pinned memory recommended): the call a host
  * makes when its tensors are on the CPU side, e.g. the reference's gloo users

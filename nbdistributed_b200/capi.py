@@ -36,11 +36,23 @@ SYMBOLS = [
     "nbd_all_reduce", "nbd_broadcast", "nbd_all_gather", "nbd_reduce_scatter", "nbd_barrier",
     "nbd_emu_all_reduce", "nbd_emu_broadcast", "nbd_emu_all_gather", "nbd_emu_reduce_scatter", "nbd_emu_barrier",
     "nbd_all_reduce_host", "nbd_emu_all_reduce_host",
+    "nbd_p2p_batch", "nbd_send", "nbd_recv", "nbd_emu_p2p_batch",
+    "nbd_broadcast_table", "nbd_emu_broadcast_table",
     "nbd_local_all_reduce_noalloc",
     "nbd_comm_last_zc_decision", "nbd_plan_query",
     "nbd_launch_count", "nbd_last_algo",
 ]
 NOALLOC_MAX_BYTES = 1 << 20
+
+
+class P2POp(C.Structure):
+    """nbd_p2p_op"""
+    _fields_ = [("kind", C.c_int), ("peer", C.c_int), ("buf", C.c_void_p), ("bytes", C.c_size_t)]
+
+
+class BcastItem(C.Structure):
+    """nbd_bcast_item"""
+    _fields_ = [("buf", C.c_void_p), ("bytes", C.c_size_t), ("root", C.c_int)]
 
 
 class NbdError(RuntimeError):
@@ -98,6 +110,12 @@ def load() -> C.CDLL:
         "nbd_emu_barrier": (i, [vp, vp]),
         "nbd_all_reduce_host": (i, [vp, vp, vp, sz, i, i, vp]),
         "nbd_emu_all_reduce_host": (i, [vp, pp, pp, sz, i, i, vp]),
+        "nbd_broadcast_table": (i, [vp, vp, i, vp]),
+        "nbd_emu_broadcast_table": (i, [vp, vp, i, vp]),
+        "nbd_p2p_batch": (i, [vp, vp, i, vp]),
+        "nbd_send": (i, [vp, vp, sz, i, vp]),
+        "nbd_recv": (i, [vp, vp, sz, i, vp]),
+        "nbd_emu_p2p_batch": (i, [vp, vp, vp, vp]),
         "nbd_local_all_reduce_noalloc": (i, [pp, pp, i, sz, i, i, vp]),
         "nbd_comm_last_zc_decision": (i, [vp]),
         "nbd_plan_query": (i, [i, sz, i, i, i, sz, C.POINTER(u64)]),
@@ -246,3 +264,37 @@ class EmuGroup:
 
     def barrier(self, stream=None) -> None:
         check(self.lib.nbd_emu_barrier(self._h, _stream_handle(stream)))
+
+    def broadcast_table(self, items, stream=None) -> None:
+        """items = list of (per-rank tensor list, root): many broadcasts in one launch
+        (nbd_emu_broadcast_table)."""
+        n = self.world_size
+        rows, ptrs = [], (C.c_void_p * n)()
+        for r in range(n):
+            arr = (BcastItem * max(1, len(items)))()
+            for k, (tensors, root) in enumerate(items):
+                t = tensors[r]
+                arr[k].buf = t.data_ptr()
+                arr[k].bytes = t.numel() * t.element_size()
+                arr[k].root = root
+            rows.append(arr)
+            ptrs[r] = C.cast(arr, C.c_void_p)
+        check(self.lib.nbd_emu_broadcast_table(self._h, ptrs, len(items), _stream_handle(stream)))
+
+    def p2p_batch(self, ops_per_rank, stream=None) -> None:
+        """ops_per_rank[r] = list of ("send" | "recv", peer, tensor) for rank r; every rank's batch
+        runs in the same cooperative launch (nbd_emu_p2p_batch)."""
+        n = self.world_size
+        arrays, ptrs, counts = [], (C.c_void_p * n)(), (C.c_int * n)()
+        for r in range(n):
+            ops = ops_per_rank[r]
+            arr = (P2POp * max(1, len(ops)))()
+            for k, (kind, peer, t) in enumerate(ops):
+                arr[k].kind = 0 if kind == "send" else 1
+                arr[k].peer = peer
+                arr[k].buf = t.data_ptr()
+                arr[k].bytes = t.numel() * t.element_size()
+            arrays.append(arr)
+            ptrs[r] = C.cast(arr, C.c_void_p)
+            counts[r] = len(ops)
+        check(self.lib.nbd_emu_p2p_batch(self._h, ptrs, counts, _stream_handle(stream)))

@@ -39,6 +39,8 @@
 namespace {
 
 constexpr const char* kBackendName = "b200";
+// broadcasts up to this size issued inside a coalescing block are packed into one table launch
+constexpr size_t kCoalesceMaxBytes = 256u << 10;
 
 bool debug_on() {
   static const bool on = [] { const char* e = std::getenv("NBDIST_B200_DEBUG"); return e && e[0] != '0'; }();
@@ -281,6 +283,14 @@ class BackendB200 : public c10d::Backend {
     check_tensor(t);
     TORCH_CHECK(opts.rootRank >= 0 && opts.rootRank < getSize(), "[b200] invalid root rank ", opts.rootRank);
     const int root = (int)opts.rootRank;
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      if (coalescing_ && (size_t)t.nbytes() <= kCoalesceMaxBytes) {  // small: one table launch at endCoalescing
+        co_bcast_.push_back({t, root});
+        co_tensors_.push_back(t);
+        return c10::intrusive_ptr<c10d::Work>();
+      }
+    }
     return run(c10d::OpType::BROADCAST, "b200:broadcast", t.get_device(), {t}, {t}, opts.asyncOp, false,
                [&](cudaStream_t s) {
                  return nbd_broadcast(comm_, t.data_ptr(), (size_t)t.nbytes(), NBD_BYTES, root, s);
@@ -407,6 +417,236 @@ class BackendB200 : public c10d::Backend {
                });
   }
 
+  // ---- point to point and the collectives built on it (csrc/nbd_p2p.cuh) ---------------------
+  // What cell code may also call on the group worker.py creates (ref:src/nbdistributed/worker.py:151,
+  // :162): dist.send / recv / isend / irecv / batch_isend_irecv, all_to_all[_single], gather,
+  // scatter, reduce.  One nbd_p2p_batch launch runs all of a rank's sends and receives of a call
+  // concurrently.  Tags are not matched (as with ProcessGroupNCCL): messages between two ranks
+  // pair up in issue order.
+  c10::intrusive_ptr<c10d::Work> send(std::vector<at::Tensor>& tensors, int dstRank, int /*tag*/) override {
+    return p2p_one(tensors, dstRank, NBD_P2P_SEND, c10d::OpType::SEND, "b200:send");
+  }
+
+  c10::intrusive_ptr<c10d::Work> recv(std::vector<at::Tensor>& tensors, int srcRank, int /*tag*/) override {
+    return p2p_one(tensors, srcRank, NBD_P2P_RECV, c10d::OpType::RECV, "b200:recv");
+  }
+
+  c10::intrusive_ptr<c10d::Work> recvAnysource(std::vector<at::Tensor>& /*tensors*/, int /*tag*/) override {
+    TORCH_CHECK(false, "[b200] recv from any source is not supported (neither does backend 'nccl'): name the source rank");
+  }
+
+  bool supportsCoalescing() const override { return true; }
+
+  // dist.batch_isend_irecv and `with dist._coalescing_manager(group, device)`: point-to-point
+  // operations issued in between are collected and run as ONE batch (so their relative order
+  // on different ranks cannot deadlock); small broadcasts are collected into one table launch.
+  void startCoalescing() override {
+    std::lock_guard<std::mutex> lk(mu_);
+    TORCH_CHECK(!coalescing_, "[b200] startCoalescing called twice");
+    coalescing_ = true;
+    co_ops_.clear();
+    co_tensors_.clear();
+    co_bcast_.clear();
+  }
+
+  c10::intrusive_ptr<c10d::Work> endCoalescing() override {
+    std::vector<nbd_p2p_op> ops;
+    std::vector<at::Tensor> tensors;
+    std::vector<CoBcast> bc;
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      TORCH_CHECK(coalescing_, "[b200] endCoalescing without startCoalescing");
+      coalescing_ = false;
+      ops.swap(co_ops_);
+      tensors.swap(co_tensors_);
+      bc.swap(co_bcast_);
+    }
+    c10::DeviceIndex dev = comm_ ? device_ : c10::cuda::current_device();
+    if (!tensors.empty()) dev = tensors[0].get_device();
+    return run(c10d::OpType::COALESCED, "b200:coalesced", dev, tensors, tensors, /*async_op=*/true, false,
+               [&](cudaStream_t s) {
+                 int rc = NBD_OK;
+                 if (!bc.empty()) {
+                   std::vector<nbd_bcast_item> items;
+                   items.reserve(bc.size());
+                   for (auto& b : bc) items.push_back(nbd_bcast_item{b.t.data_ptr(), (size_t)b.t.nbytes(), b.root});
+                   rc = nbd_broadcast_table(comm_, items.data(), (int)items.size(), s);
+                 }
+                 if (rc == NBD_OK && !ops.empty()) rc = nbd_p2p_batch(comm_, ops.data(), (int)ops.size(), s);
+                 return rc;
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> alltoall_base(at::Tensor& out, at::Tensor& in, std::vector<int64_t>& outSplits,
+                                               std::vector<int64_t>& inSplits, const c10d::AllToAllOptions& opts) override {
+    check_tensor(out);
+    check_tensor(in);
+    TORCH_CHECK(out.scalar_type() == in.scalar_type(), "[b200] all_to_all: output and input dtypes differ");
+    const int N = getSize(), me = getRank();
+    auto offsets = [&](const at::Tensor& t, const std::vector<int64_t>& splits, std::vector<int64_t>* off, std::vector<int64_t>* len) {
+      const int64_t row = t.dim() > 0 && t.size(0) > 0 ? t.numel() / t.size(0) : 1;  // elements per index of dim 0
+      off->assign(N, 0);
+      len->assign(N, 0);
+      if (splits.empty()) {
+        TORCH_CHECK(t.dim() > 0 && t.size(0) % N == 0, "[b200] all_to_all_single: dim 0 must be divisible by world_size");
+        for (int r = 0; r < N; ++r) {
+          (*len)[r] = t.size(0) / N * row;
+          (*off)[r] = r * (*len)[r];
+        }
+      } else {
+        TORCH_CHECK((int)splits.size() == N, "[b200] all_to_all_single: split sizes must have world_size entries");
+        int64_t acc = 0;
+        for (int r = 0; r < N; ++r) {
+          (*off)[r] = acc * row;
+          (*len)[r] = splits[r] * row;
+          acc += splits[r];
+        }
+        TORCH_CHECK(acc == (t.dim() > 0 ? t.size(0) : 0), "[b200] all_to_all_single: split sizes do not add up to dim 0");
+      }
+    };
+    std::vector<int64_t> ooff, olen, ioff, ilen;
+    offsets(out, outSplits, &ooff, &olen);
+    offsets(in, inSplits, &ioff, &ilen);
+    TORCH_CHECK(olen[me] == ilen[me], "[b200] all_to_all_single: this rank's own input and output splits differ");
+    const size_t es = in.element_size();
+    return run(c10d::OpType::ALLTOALL_BASE, "b200:all_to_all_single", in.get_device(), {in}, {out}, opts.asyncOp, false,
+               [&](cudaStream_t s) {
+                 std::vector<nbd_p2p_op> ops;
+                 for (int k = 1; k < N; ++k) {  // rotated start: no peer is hit by every sender at once
+                   const int p = (me + k) % N;
+                   ops.push_back({NBD_P2P_SEND, p, (char*)in.data_ptr() + ioff[p] * es, (size_t)ilen[p] * es});
+                 }
+                 for (int k = 1; k < N; ++k) {
+                   const int p = (me - k + N) % N;
+                   ops.push_back({NBD_P2P_RECV, p, (char*)out.data_ptr() + ooff[p] * es, (size_t)olen[p] * es});
+                 }
+                 if (ilen[me] > 0 && (char*)out.data_ptr() + ooff[me] * es != (char*)in.data_ptr() + ioff[me] * es)
+                   if (cudaMemcpyAsync((char*)out.data_ptr() + ooff[me] * es, (char*)in.data_ptr() + ioff[me] * es,
+                                       (size_t)ilen[me] * es, cudaMemcpyDeviceToDevice, s) != cudaSuccess)
+                     return (int)NBD_ERR_CUDA;
+                 return nbd_p2p_batch(comm_, ops.data(), (int)ops.size(), s);
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> alltoall(std::vector<at::Tensor>& outs, std::vector<at::Tensor>& ins,
+                                          const c10d::AllToAllOptions& opts) override {
+    const int N = getSize(), me = getRank();
+    TORCH_CHECK((int)outs.size() == N && (int)ins.size() == N, "[b200] all_to_all: tensor lists must have world_size entries");
+    for (int r = 0; r < N; ++r) {
+      check_tensor(outs[r]);
+      check_tensor(ins[r]);
+    }
+    TORCH_CHECK(outs[me].nbytes() == ins[me].nbytes(), "[b200] all_to_all: this rank's own input and output sizes differ");
+    std::vector<at::Tensor> all(ins.begin(), ins.end());
+    all.insert(all.end(), outs.begin(), outs.end());
+    return run(c10d::OpType::ALLTOALL, "b200:all_to_all", ins[0].get_device(), all, all, opts.asyncOp, false,
+               [&](cudaStream_t s) {
+                 std::vector<nbd_p2p_op> ops;
+                 for (int k = 1; k < N; ++k) {
+                   const int p = (me + k) % N;
+                   ops.push_back({NBD_P2P_SEND, p, ins[p].data_ptr(), (size_t)ins[p].nbytes()});
+                 }
+                 for (int k = 1; k < N; ++k) {
+                   const int p = (me - k + N) % N;
+                   ops.push_back({NBD_P2P_RECV, p, outs[p].data_ptr(), (size_t)outs[p].nbytes()});
+                 }
+                 if (ins[me].nbytes() > 0 && outs[me].data_ptr() != ins[me].data_ptr())
+                   if (cudaMemcpyAsync(outs[me].data_ptr(), ins[me].data_ptr(), (size_t)ins[me].nbytes(), cudaMemcpyDeviceToDevice, s) !=
+                       cudaSuccess)
+                     return (int)NBD_ERR_CUDA;
+                 return nbd_p2p_batch(comm_, ops.data(), (int)ops.size(), s);
+               });
+  }
+
+  c10::intrusive_ptr<c10d::Work> gather(std::vector<std::vector<at::Tensor>>& outs, std::vector<at::Tensor>& ins,
+                                        const c10d::GatherOptions& opts) override {
+    const int N = getSize(), me = getRank(), root = (int)opts.rootRank;
+    TORCH_CHECK(ins.size() == 1, "[b200] gather expects one input tensor");
+    TORCH_CHECK(root >= 0 && root < N, "[b200] invalid root rank ", root);
+    check_tensor(ins[0]);
+    std::vector<at::Tensor> all{ins[0]};
+    if (me == root) {
+      TORCH_CHECK(outs.size() == 1 && (int)outs[0].size() == N, "[b200] gather: the root needs world_size output tensors");
+      for (auto& o : outs[0]) {
+        check_tensor(o);
+        TORCH_CHECK(o.nbytes() == ins[0].nbytes() && o.scalar_type() == ins[0].scalar_type(),
+                    "[b200] gather: every output tensor must match the input's dtype and size");
+        all.push_back(o);
+      }
+    } else {
+      TORCH_CHECK(outs.empty() || outs[0].empty(), "[b200] gather: only the root passes output tensors");
+    }
+    return run(c10d::OpType::GATHER, "b200:gather", ins[0].get_device(), all, all, opts.asyncOp, false, [&](cudaStream_t s) {
+      std::vector<nbd_p2p_op> ops;
+      if (me == root) {
+        for (int k = 1; k < N; ++k) {
+          const int p = (me + k) % N;
+          ops.push_back({NBD_P2P_RECV, p, outs[0][p].data_ptr(), (size_t)outs[0][p].nbytes()});
+        }
+        if (ins[0].nbytes() > 0 && outs[0][me].data_ptr() != ins[0].data_ptr())
+          if (cudaMemcpyAsync(outs[0][me].data_ptr(), ins[0].data_ptr(), (size_t)ins[0].nbytes(), cudaMemcpyDeviceToDevice, s) !=
+              cudaSuccess)
+            return (int)NBD_ERR_CUDA;
+      } else {
+        ops.push_back({NBD_P2P_SEND, root, ins[0].data_ptr(), (size_t)ins[0].nbytes()});
+      }
+      return nbd_p2p_batch(comm_, ops.data(), (int)ops.size(), s);
+    });
+  }
+
+  c10::intrusive_ptr<c10d::Work> scatter(std::vector<at::Tensor>& outs, std::vector<std::vector<at::Tensor>>& ins,
+                                         const c10d::ScatterOptions& opts) override {
+    const int N = getSize(), me = getRank(), root = (int)opts.rootRank;
+    TORCH_CHECK(outs.size() == 1, "[b200] scatter expects one output tensor");
+    TORCH_CHECK(root >= 0 && root < N, "[b200] invalid root rank ", root);
+    check_tensor(outs[0]);
+    std::vector<at::Tensor> all{outs[0]};
+    if (me == root) {
+      TORCH_CHECK(ins.size() == 1 && (int)ins[0].size() == N, "[b200] scatter: the root needs world_size input tensors");
+      for (auto& t : ins[0]) {
+        check_tensor(t);
+        TORCH_CHECK(t.nbytes() == outs[0].nbytes() && t.scalar_type() == outs[0].scalar_type(),
+                    "[b200] scatter: every input tensor must match the output's dtype and size");
+        all.push_back(t);
+      }
+    } else {
+      TORCH_CHECK(ins.empty() || ins[0].empty(), "[b200] scatter: only the root passes input tensors");
+    }
+    return run(c10d::OpType::SCATTER, "b200:scatter", outs[0].get_device(), all, all, opts.asyncOp, false, [&](cudaStream_t s) {
+      std::vector<nbd_p2p_op> ops;
+      if (me == root) {
+        for (int k = 1; k < N; ++k) {
+          const int p = (me + k) % N;
+          ops.push_back({NBD_P2P_SEND, p, ins[0][p].data_ptr(), (size_t)ins[0][p].nbytes()});
+        }
+        if (outs[0].nbytes() > 0 && outs[0].data_ptr() != ins[0][me].data_ptr())
+          if (cudaMemcpyAsync(outs[0].data_ptr(), ins[0][me].data_ptr(), (size_t)outs[0].nbytes(), cudaMemcpyDeviceToDevice, s) !=
+              cudaSuccess)
+            return (int)NBD_ERR_CUDA;
+      } else {
+        ops.push_back({NBD_P2P_RECV, root, outs[0].data_ptr(), (size_t)outs[0].nbytes()});
+      }
+      return nbd_p2p_batch(comm_, ops.data(), (int)ops.size(), s);
+    });
+  }
+
+  // dist.reduce: the root's tensor receives the reduction; the other ranks' tensors are left
+  // untouched (they reduce into a scratch tensor), as with gloo.
+  c10::intrusive_ptr<c10d::Work> reduce(std::vector<at::Tensor>& tensors, const c10d::ReduceOptions& opts) override {
+    TORCH_CHECK(tensors.size() == 1, "[b200] reduce expects exactly one tensor");
+    auto& t = tensors[0];
+    check_tensor(t);
+    const int root = (int)opts.rootRank;
+    TORCH_CHECK(root >= 0 && root < getSize(), "[b200] invalid root rank ", root);
+    const int dtype = to_nbd_dtype(t.scalar_type(), true), op = to_nbd_op(opts.reduceOp);
+    return run(c10d::OpType::REDUCE, "b200:reduce", t.get_device(), {t}, {t}, opts.asyncOp, false, [&](cudaStream_t s) {
+      if (getRank() == root) return nbd_all_reduce(comm_, t.data_ptr(), t.data_ptr(), (size_t)t.numel(), dtype, op, s);
+      at::Tensor scratch = at::empty_like(t);
+      note_stream(scratch);
+      return nbd_all_reduce(comm_, t.data_ptr(), scratch.data_ptr(), (size_t)t.numel(), dtype, op, s);
+    });
+  }
+
   c10::intrusive_ptr<c10d::Work> barrier(const c10d::BarrierOptions& opts) override {
     c10::DeviceIndex dev = device_;
     if (!comm_) {
@@ -518,6 +758,31 @@ class BackendB200 : public c10d::Backend {
   void set_inline_sync_ops(bool v) { inline_sync_ops_ = v; }
 
  private:
+  struct CoBcast {
+    at::Tensor t;
+    int root;
+  };
+
+  c10::intrusive_ptr<c10d::Work> p2p_one(std::vector<at::Tensor>& tensors, int peer, int kind, c10d::OpType type, const char* title) {
+    TORCH_CHECK(tensors.size() == 1, "[b200] send/recv expect exactly one tensor");
+    auto& t = tensors[0];
+    check_tensor(t);
+    TORCH_CHECK(peer >= 0 && peer < getSize() && peer != getRank(), "[b200] send/recv: peer ", peer,
+                " is not another rank of this group");
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      if (coalescing_) {  // collected; endCoalescing launches the whole batch and returns its Work
+        co_ops_.push_back({kind, peer, t.data_ptr(), (size_t)t.nbytes()});
+        co_tensors_.push_back(t);
+        return c10::intrusive_ptr<c10d::Work>();
+      }
+    }
+    return run(type, title, t.get_device(), {t}, {t}, /*async_op=*/true, false, [&](cudaStream_t s) {
+      nbd_p2p_op op = {kind, peer, t.data_ptr(), (size_t)t.nbytes()};
+      return nbd_p2p_batch(comm_, &op, 1, s);
+    });
+  }
+
   static int64_t shutdown_wait_ms() {
     const char* e = std::getenv("NBDIST_B200_SHUTDOWN_WAIT_MS");
     return e ? std::atoll(e) : 2000;
@@ -625,6 +890,10 @@ class BackendB200 : public c10d::Backend {
   int mem_seq_ = 0;
   std::shared_ptr<std::atomic<bool>> alive_ = std::make_shared<std::atomic<bool>>(true);
   std::vector<std::pair<std::string, uint64_t>> tunables_;
+  bool coalescing_ = false;
+  std::vector<nbd_p2p_op> co_ops_;
+  std::vector<at::Tensor> co_tensors_;
+  std::vector<CoBcast> co_bcast_;
 };
 
 c10::intrusive_ptr<c10d::Backend> create_backend(const c10::intrusive_ptr<c10d::Store>& store, int rank, int size,

@@ -59,6 +59,7 @@ struct RankCtx {
   u64 half_bytes;   // bytes in one staging half (multiple of 16)
   u64 timeout_ns;   // 0 = never
   u64 ll_off;       // offset of the LL area inside every rank's staging (0: no LL area)
+  u64 p2p_off;      // offset of the point-to-point area (nbd_p2p.cuh) from every rank's staging base (0: none)
 };
 
 // LL ("low latency") area at the tail of the staging region: for each parity, one slot per
@@ -128,6 +129,8 @@ struct LocalBlock {
   ZcDecision dec;
   u64 imp[kMaxRanks][kMaxExports];  // imp[p][slot]: rank p's exported allocation mapped here, or 0
   u64 prev_desc[kMaxRanks][6];      // every rank's descriptor of the previous agreement
+  u64 p2p_tx[kMaxRanks];            // point-to-point chunks sent to rank p so far (nbd_p2p.cuh)
+  u64 p2p_rx[kMaxRanks];            // ... and received from rank p
 };
 
 // Operation descriptors for the symmetric-use check live in flag rows no grid ever reaches
@@ -146,6 +149,7 @@ struct OpParams {
   int avg;          // 1: divide the sum by world (NBD_AVG)
   int zc_mode;      // 0: unconditional; 1: zero-copy kernel, run only if the agreed decision is ok
                     // (buffers come from the decision); 2: staged kernel, run only if it is not
+  int depth;        // tile pipeline (nbd_pipe.cuh): staging slots per CTA
 };
 
 // ---------------------------------------------------------------------------

@@ -129,6 +129,9 @@ struct nbd_comm {
   uint64_t t_nvls_min = 0;      // smallest message for the multicast kernels
   uint64_t t_pipe = 0;          // 1: force the tile-pipeline kernels (P2P transport) where they apply; 2: never
   uint64_t t_pipe_tile = 0;     // tile bytes per CTA per round (0 = planner's choice)
+  uint64_t t_pipe_depth = 0;    // staging slots per CTA (0 = default)
+  uint64_t t_pipe_mode = 0;     // bit 1: two reducing groups; bit 2: 8 loads in flight per thread (0 = default)
+  uint64_t t_nvls_bcast = 0;    // 1: broadcast through multimem.st where multicast is set up
   uint64_t t_debug_mute = 0;    // tests: rank (value - 1) of an emulated group never signals its peers
 };
 

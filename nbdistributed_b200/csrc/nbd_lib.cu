@@ -13,6 +13,7 @@
 #include <string.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 #include <map>
@@ -24,6 +25,8 @@
 #include "nbd_kernel_table.h"
 #include "nbd_kernels.cuh"
 #include "nbd_pipe.cuh"
+#include "nbd_p2p.cuh"
+#include "nbd_table.cuh"
 
 // ---------------------------------------------------------------------------
 // errors
@@ -68,7 +71,7 @@ static int alloc_rank(nbd_comm* c, size_t stage_bytes) {
   }
   stage_bytes = (stage_bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
   c->stage_bytes = stage_bytes;
-  c->arena_bytes = kFlagBytes + stage_bytes;
+  c->arena_bytes = kFlagBytes + stage_bytes + kP2PAreaBytes;  // flags | staging (halves + LL) | point-to-point area
   cudaDeviceProp prop;
   NBD_CUDA(cudaGetDeviceProperties(&prop, c->device));
   c->num_sms = prop.multiProcessorCount;
@@ -120,6 +123,7 @@ static void fill_ctx(nbd_comm* c) {
   x.mbox = c->mbox_dev;
   // the last MiB of staging is the LL area; the two pipeline halves share the rest
   x.ll_off = c->stage_bytes - kLLAreaBytes;
+  x.p2p_off = c->stage_bytes;
   x.half_bytes = ((c->stage_bytes - kLLAreaBytes) / 2) / kUnit * kUnit;
   x.timeout_ns = c->timeout_ms * 1000000ull;
 }
@@ -353,6 +357,9 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "pipe")) return &c->t_pipe;
   if (!strcmp(name, "pipe_tile_bytes")) return &c->t_pipe_tile;
   if (!strcmp(name, "debug_mute_rank")) return &c->t_debug_mute;
+  if (!strcmp(name, "pipe_depth")) return &c->t_pipe_depth;
+  if (!strcmp(name, "pipe_mode")) return &c->t_pipe_mode;
+  if (!strcmp(name, "nvls_bcast")) return &c->t_nvls_bcast;
   return nullptr;
 }
 
@@ -608,7 +615,7 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
 // kPipeDepth staging slots.  Tiles are 16..256 KiB: small enough that copy-in, reduction and
 // copy-out of neighbouring tiles overlap and a flag costs one tile of latency, large enough that
 // the TMA rings and the 448 reducing threads have work.  capacity = staging bytes per rank.
-static const u64 kPipeTileMin = 16ull << 10, kPipeTileMax = 256ull << 10;
+static const u64 kPipeTileMin = 16ull << 10, kPipeTileMax = 1ull << 20, kPipeTileDef = 256ull << 10;
 
 static int plan_pipe(nbd_comm* c, u64 bytes, u64 capacity, int emu_world, Plan* out) {
   Plan p;
@@ -621,11 +628,15 @@ static int plan_pipe(nbd_comm* c, u64 bytes, u64 capacity, int emu_world, Plan* 
   u64 G = ceil_div(bytes, kPipeTileMin);
   if (G < 1) G = 1;
   if (G > gmax) G = gmax;
+  const u64 depth = c->t_pipe_depth ? (c->t_pipe_depth < 2 ? 2 : (c->t_pipe_depth > 8 ? 8 : c->t_pipe_depth)) : (u64)kPipeDepth;
   u64 tile = c->t_pipe_tile ? c->t_pipe_tile : ceil_div(bytes, G * 4);
-  if (tile < kPipeTileMin && !c->t_pipe_tile) tile = kPipeTileMin;
+  if (!c->t_pipe_tile) {
+    if (tile < kPipeTileMin) tile = kPipeTileMin;
+    if (tile > kPipeTileDef) tile = kPipeTileDef;
+  }
   if (tile > kPipeTileMax) tile = kPipeTileMax;
   tile = ceil_div(tile, 128) * 128;
-  const u64 cap_tile = floor_to(capacity / (G * kPipeDepth), 128);
+  const u64 cap_tile = floor_to(capacity / (G * depth), 128);
   if (tile > cap_tile) tile = cap_tile;
   if (tile < 128) return fail(NBD_ERR_INVALID_ARGUMENT, "staging of %llu bytes is too small for the tile pipeline (%llu CTAs)",
                              (unsigned long long)capacity, (unsigned long long)G);
@@ -633,6 +644,8 @@ static int plan_pipe(nbd_comm* c, u64 bytes, u64 capacity, int emu_world, Plan* 
   p.op.chunk_bytes = tile;
   p.op.nchunks = (u32)ceil_div(ceil_div(bytes, kUnit) * kUnit, G * tile);
   p.op.world = c->world;
+  p.op.depth = (int)depth;
+  p.op.algo = (int)(c->t_pipe_mode & 6);  // callers add bit 0 (open with a barrier) for arena staging
   p.nblocks = (int)G;
   *out = p;
   return NBD_OK;
@@ -673,8 +686,11 @@ static bool nvls_reduce_wanted(const nbd_comm* c, u64 bytes, int dtype, int op) 
          bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsReduceMin);
 }
 
+// Broadcast over multimem.st is correct but, measured at 8xB200, slower than the scatter kernel at
+// every size (256 MiB: 366 vs 535 GB/s; one source feeding the switch's replication), so it only
+// runs on request ("nvls_bcast" = 1).
 static bool nvls_bcast_wanted(const nbd_comm* c, u64 bytes) {
-  return c->nvls.enabled && !c->t_nvls_off && bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsBcastMin);
+  return c->nvls.enabled && !c->t_nvls_off && c->t_nvls_bcast && bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsBcastMin);
 }
 
 // P2P tile pipeline: only on request ("pipe" = 1) until measurements say where it wins
@@ -698,7 +714,7 @@ static int pipe_all_reduce(nbd_comm* c, const void* send, void* recv, u64 bytes,
   if (rc != NBD_OK) return rc;
   p.op.op = op;
   p.op.avg = (op == NBD_AVG);
-  p.op.algo = mc ? 0 : 1;  // arena staging is shared with the chunked kernels: open with a barrier
+  p.op.algo |= mc ? 0 : 1;  // arena staging is shared with the chunked kernels: open with a barrier
   PackPipe<1> pk;
   fill_pipe(pk, c, send, recv, mc);
   c->last_algo = mc ? "ar_nvls" : "ar_pipe";
@@ -711,7 +727,7 @@ static int pipe_broadcast(nbd_comm* c, void* buf, u64 bytes, int root, bool mc, 
   int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.bytes : 2 * c->ctx.half_bytes, 0, &p);
   if (rc != NBD_OK) return rc;
   p.op.root = root;
-  p.op.algo = mc ? 0 : 1;
+  p.op.algo |= mc ? 0 : 1;
   PackPipe<1> pk;
   fill_pipe(pk, c, buf, buf, mc);
   c->last_algo = mc ? "bcast_nvls" : "bcast_pipe";
@@ -1283,7 +1299,7 @@ int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* re
     if ((rc = plan_pipe(c0, bytes, 2 * c0->ctx.half_bytes, g->world, &p)) != NBD_OK) return rc;
     p.op.op = op;
     p.op.avg = (op == NBD_AVG);
-    p.op.algo = 1;
+    p.op.algo |= 1;
     PackPipe<kMaxRanks> pk;
     memset(&pk, 0, sizeof(pk));
     for (int r = 0; r < g->world; ++r) {
@@ -1384,7 +1400,7 @@ int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count, int dtype
     Plan p;
     if ((rc = plan_pipe(c0, (u64)count * es, 2 * c0->ctx.half_bytes, g->world, &p)) != NBD_OK) return rc;
     p.op.root = root;
-    p.op.algo = 1;
+    p.op.algo |= 1;
     PackPipe<kMaxRanks> pk;
     memset(&pk, 0, sizeof(pk));
     for (int r = 0; r < g->world; ++r) {
@@ -1423,6 +1439,284 @@ int nbd_emu_barrier(nbd_comm_t any, void* stream) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// broadcast tables (nbd_table.cuh): many small broadcasts, one launch, one flag barrier
+// ---------------------------------------------------------------------------
+namespace {
+
+// Launches items [i0, i1) as one table.  bufs[r][k]: rank r's buffer of item k (real rank: r = 0).
+template <int NCTX>
+int launch_table(nbd_comm* c0, const RankCtx* ctx, int world, const nbd_bcast_item* const* items, int i0, int i1, cudaStream_t s) {
+  static thread_local PackTable<NCTX> pk;  // ~10 KiB: keep it off the stack
+  memset(&pk, 0, sizeof(pk));
+  for (int r = 0; r < NCTX && r < world; ++r) pk.ctx[r] = ctx[r];
+  u64 units = 0;
+  for (int k = i0; k < i1; ++k) {
+    const int j = k - i0;
+    pk.d.first[j] = (u32)units;
+    pk.d.bytes[j] = (u64)items[0][k].bytes;
+    pk.d.root[j] = (unsigned char)items[0][k].root;
+    for (int r = 0; r < NCTX && r < world; ++r) pk.buf[r][j] = (char*)items[r][k].buf;
+    units += ceil_div((u64)items[0][k].bytes, kUnit);
+  }
+  pk.d.nitems = i1 - i0;
+  pk.d.first[pk.d.nitems] = (u32)units;
+  const int nblocks = pick_blocks(c0, units, NCTX == 1 ? 0 : world);
+  void* args[1] = {(void*)&pk};
+  if (NCTX == 1) {
+    NBD_CUDA(cudaLaunchKernel((const void*)k_bcast_table<NCTX>, dim3(nblocks, 1, 1), dim3(kThreads, 1, 1), args, 0, s));
+  } else {
+    NBD_CUDA(cudaLaunchCooperativeKernel((const void*)k_bcast_table<NCTX>, dim3(nblocks, world, 1), dim3(kThreads, 1, 1), args, 0, s));
+  }
+  g_launches.fetch_add(1);
+  return NBD_OK;
+}
+
+// Cuts the item list into tables (<= kTableMax items, packed size <= one staging half); an item
+// too large for a table is handed to `big` (the ordinary broadcast).
+template <typename Table, typename Big>
+int run_tables(const nbd_comm* c0, const nbd_bcast_item* items, int n, int world, Table table, Big big) {
+  const u64 cap_units = c0->ctx.half_bytes / kUnit;
+  int i0 = 0;
+  u64 units = 0;
+  for (int k = 0; k <= n; ++k) {
+    const u64 u = k < n ? ceil_div((u64)items[k].bytes, kUnit) : 0;
+    const bool oversize = k < n && u > cap_units / 2;
+    if (k == n || oversize || k - i0 == kTableMax || units + u > cap_units) {
+      if (k > i0) {
+        int rc = table(i0, k);
+        if (rc != NBD_OK) return rc;
+      }
+      i0 = k;
+      units = 0;
+      if (oversize) {
+        int rc = big(k);
+        if (rc != NBD_OK) return rc;
+        i0 = k + 1;
+        continue;
+      }
+    }
+    units += u;
+  }
+  (void)world;
+  return NBD_OK;
+}
+
+int check_items(const nbd_bcast_item* items, int n, int world) {
+  for (int k = 0; k < n; ++k) {
+    if (items[k].root < 0 || items[k].root >= world) return fail(NBD_ERR_INVALID_ARGUMENT, "table item %d: root %d not in [0,%d)", k, items[k].root, world);
+    if (items[k].bytes && !items[k].buf) return fail(NBD_ERR_INVALID_ARGUMENT, "table item %d: NULL buffer", k);
+  }
+  return NBD_OK;
+}
+
+}  // namespace
+
+extern "C" int nbd_broadcast_table(nbd_comm_t c, const nbd_bcast_item* items, int n, void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_broadcast_table with emulated communicators");
+  if (n < 0 || (n > 0 && !items)) return fail(NBD_ERR_INVALID_ARGUMENT, "bad item list");
+  if ((rc = check_items(items, n, c->world)) != NBD_OK) return rc;
+  if (c->world == 1 || n == 0) return NBD_OK;
+  DeviceGuard g(c->device);
+  std::vector<nbd_bcast_item> live;  // empty broadcasts are no-ops
+  for (int k = 0; k < n; ++k)
+    if (items[k].bytes) live.push_back(items[k]);
+  const nbd_bcast_item* rows[1] = {live.data()};
+  rc = run_tables(
+      c, live.data(), (int)live.size(), c->world,
+      [&](int i0, int i1) { return launch_table<1>(c, &c->ctx, c->world, rows, i0, i1, (cudaStream_t)stream); },
+      [&](int k) { return nbd_broadcast(c, live[(size_t)k].buf, live[(size_t)k].bytes, NBD_BYTES, live[(size_t)k].root, stream); });
+  c->last_algo = "bcast_table";
+  return rc;
+}
+
+extern "C" int nbd_emu_broadcast_table(nbd_comm_t any, const nbd_bcast_item* const* items, int n, void* stream) {
+  if (!any) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (!any->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "not an emulated communicator");
+  if (n < 0 || (n > 0 && !items)) return fail(NBD_ERR_INVALID_ARGUMENT, "bad item list");
+  EmuGroup* g = any->group;
+  nbd_comm* c0 = g->comms[0];
+  int rc;
+  RankCtx ctx[kMaxRanks];
+  for (int r = 0; r < g->world; ++r) {
+    if ((rc = check_usable(g->comms[r])) != NBD_OK) return rc;
+    if (!items[r]) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL item list for rank %d", r);
+    if ((rc = check_items(items[r], n, g->world)) != NBD_OK) return rc;
+    ctx[r] = g->comms[r]->ctx;
+    for (int k = 0; k < n; ++k)
+      if (items[r][k].bytes != items[0][k].bytes || items[r][k].root != items[0][k].root)
+        return fail(NBD_ERR_MISMATCH, "table item %d differs between rank 0 and rank %d", k, r);
+  }
+  if (g->world == 1 || n == 0) return NBD_OK;
+  DeviceGuard dg(c0->device);
+  mute_rank(g, ctx);
+  // drop empty items from every rank's row alike
+  std::vector<nbd_bcast_item> live[kMaxRanks];
+  const nbd_bcast_item* rows[kMaxRanks] = {};
+  for (int r = 0; r < g->world; ++r) {
+    for (int k = 0; k < n; ++k)
+      if (items[0][k].bytes) live[r].push_back(items[r][k]);
+    rows[r] = live[r].data();
+  }
+  rc = run_tables(
+      c0, live[0].data(), (int)live[0].size(), g->world,
+      [&](int i0, int i1) { return launch_table<kMaxRanks>(c0, ctx, g->world, rows, i0, i1, (cudaStream_t)stream); },
+      [&](int k) {
+        void* bufs[kMaxRanks];
+        for (int r = 0; r < g->world; ++r) bufs[r] = live[r][(size_t)k].buf;
+        return nbd_emu_broadcast(any, bufs, live[0][(size_t)k].bytes, NBD_BYTES, live[0][(size_t)k].root, stream);
+      });
+  set_algo(c0, "bcast_table");
+  return rc;
+}
+
+// ---------------------------------------------------------------------------
+// point-to-point batches (nbd_p2p.cuh)
+// ---------------------------------------------------------------------------
+namespace {
+
+struct LaneList {
+  int peer = 0, send = 0;
+  std::vector<P2PMsg> msgs;
+};
+
+// Groups a rank's operations into lanes (direction, peer), messages in issue order.  Local
+// copies (peer == rank) are not part of the C ABI: callers do those themselves.
+int build_lanes(int rank, int world, const nbd_p2p_op* ops, int nops, std::vector<LaneList>* lanes) {
+  for (int i = 0; i < nops; ++i) {
+    const nbd_p2p_op& o = ops[i];
+    if (o.kind != NBD_P2P_SEND && o.kind != NBD_P2P_RECV) return fail(NBD_ERR_INVALID_ARGUMENT, "p2p op %d: kind %d is neither send nor recv", i, o.kind);
+    if (o.peer < 0 || o.peer >= world || o.peer == rank)
+      return fail(NBD_ERR_INVALID_ARGUMENT, "p2p op %d: peer %d is not another rank of this %d-rank group", i, o.peer, world);
+    if (o.bytes == 0) continue;  // both sides skip empty messages
+    if (!o.buf) return fail(NBD_ERR_INVALID_ARGUMENT, "p2p op %d: NULL buffer", i);
+    LaneList* L = nullptr;
+    for (auto& l : *lanes)
+      if (l.peer == o.peer && l.send == (o.kind == NBD_P2P_SEND)) L = &l;
+    if (!L) {
+      lanes->emplace_back();
+      L = &lanes->back();
+      L->peer = o.peer;
+      L->send = (o.kind == NBD_P2P_SEND);
+    }
+    L->msgs.push_back(P2PMsg{(char*)o.buf, (u64)o.bytes});
+  }
+  return NBD_OK;
+}
+
+// CTAs per lane: a power of two (it must divide the 32 virtual spans), as many as stay co-resident.
+int lane_ctas(int cap, int nlanes) {
+  int g = 1;
+  while (g * 2 <= kP2PVirt && g * 2 * nlanes <= cap) g *= 2;
+  return g;
+}
+
+// Fills launch `round` (messages [round*kP2PLaneMsgs, +kP2PLaneMsgs) of every lane); returns CTAs used.
+int fill_p2p_rank(P2PRank* pr, const std::vector<LaneList>& lanes, size_t round, int g) {
+  memset(pr, 0, sizeof(*pr));
+  int cta = 0;
+  for (const auto& l : lanes) {
+    const size_t first = round * kP2PLaneMsgs;
+    if (first >= l.msgs.size()) continue;
+    P2PLane& L = pr->lane[pr->nlanes++];
+    L.peer = l.peer;
+    L.send = l.send;
+    L.cta0 = cta;
+    L.nctas = g;
+    cta += g;
+    for (size_t m = first; m < l.msgs.size() && m < first + kP2PLaneMsgs; ++m) L.msg[L.nmsgs++] = l.msgs[m];
+  }
+  return cta;
+}
+
+size_t p2p_rounds(const std::vector<LaneList>& lanes) {
+  size_t r = 0;
+  for (const auto& l : lanes) r = std::max(r, (l.msgs.size() + kP2PLaneMsgs - 1) / kP2PLaneMsgs);
+  return r;
+}
+
+}  // namespace
+
+extern "C" int nbd_p2p_batch(nbd_comm_t c, const nbd_p2p_op* ops, int nops, void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_p2p_batch with emulated communicators");
+  if (nops < 0 || (nops > 0 && !ops)) return fail(NBD_ERR_INVALID_ARGUMENT, "bad p2p op list");
+  std::vector<LaneList> lanes;
+  if ((rc = build_lanes(c->rank, c->world, ops, nops, &lanes)) != NBD_OK) return rc;
+  if (lanes.empty()) return NBD_OK;
+  if (lanes.size() > (size_t)kP2PMaxLanes) return fail(NBD_ERR_INTERNAL, "too many p2p lanes");
+  DeviceGuard g(c->device);
+  int cap = c->num_sms * kMinBlocksPerSM;
+  if (c->t_blocks && (int)c->t_blocks < cap) cap = (int)c->t_blocks;
+  const int gl = lane_ctas(cap, (int)lanes.size());
+  const size_t rounds = p2p_rounds(lanes);
+  for (size_t r = 0; r < rounds; ++r) {
+    PackP2P<1> pk;
+    memset(&pk, 0, sizeof(pk));
+    pk.ctx[0] = c->ctx;
+    const int ctas = fill_p2p_rank(&pk.r[0], lanes, r, gl);
+    if (ctas == 0) continue;
+    void* args[1] = {(void*)&pk};
+    NBD_CUDA(cudaLaunchKernel((const void*)k_p2p_batch<1>, dim3(ctas, 1, 1), dim3(kThreads, 1, 1), args, 0, (cudaStream_t)stream));
+    g_launches.fetch_add(1);
+  }
+  c->last_algo = "p2p_batch";
+  return NBD_OK;
+}
+
+extern "C" int nbd_send(nbd_comm_t c, const void* buf, size_t bytes, int peer, void* stream) {
+  nbd_p2p_op op = {NBD_P2P_SEND, peer, const_cast<void*>(buf), bytes};
+  return nbd_p2p_batch(c, &op, 1, stream);
+}
+
+extern "C" int nbd_recv(nbd_comm_t c, void* buf, size_t bytes, int peer, void* stream) {
+  nbd_p2p_op op = {NBD_P2P_RECV, peer, buf, bytes};
+  return nbd_p2p_batch(c, &op, 1, stream);
+}
+
+extern "C" int nbd_emu_p2p_batch(nbd_comm_t any, const nbd_p2p_op* const* ops, const int* nops, void* stream) {
+  if (!any) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (!any->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "not an emulated communicator");
+  if (!ops || !nops) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL op lists");
+  EmuGroup* g = any->group;
+  nbd_comm* c0 = g->comms[0];
+  DeviceGuard dg(c0->device);
+  std::vector<LaneList> lanes[kMaxRanks];
+  size_t maxl = 0, rounds = 0;
+  int rc;
+  for (int r = 0; r < g->world; ++r) {
+    if ((rc = check_usable(g->comms[r])) != NBD_OK) return rc;
+    if ((rc = build_lanes(r, g->world, ops[r], nops[r], &lanes[r])) != NBD_OK) return rc;
+    maxl = std::max(maxl, lanes[r].size());
+    rounds = std::max(rounds, p2p_rounds(lanes[r]));
+  }
+  if (maxl == 0) return NBD_OK;
+  int cap = c0->num_sms * kMinBlocksPerSM / g->world;
+  if (c0->t_blocks && (int)c0->t_blocks < cap) cap = (int)c0->t_blocks;
+  if (cap < 1) cap = 1;
+  if ((int)maxl > cap) return fail(NBD_ERR_UNSUPPORTED, "%zu lanes per emulated rank do not fit %d co-resident CTAs", maxl, cap);
+  const int gl = lane_ctas(cap, (int)maxl);
+  for (size_t rd = 0; rd < rounds; ++rd) {
+    PackP2P<kMaxRanks> pk;
+    memset(&pk, 0, sizeof(pk));
+    int ctas = 0;
+    for (int r = 0; r < g->world; ++r) {
+      pk.ctx[r] = g->comms[r]->ctx;
+      ctas = std::max(ctas, fill_p2p_rank(&pk.r[r], lanes[r], rd, gl));
+    }
+    if (ctas == 0) continue;
+    void* args[1] = {(void*)&pk};
+    NBD_CUDA(cudaLaunchCooperativeKernel((const void*)k_p2p_batch<kMaxRanks>, dim3(ctas, g->world, 1), dim3(kThreads, 1, 1), args, 0,
+                                         (cudaStream_t)stream));
+    g_launches.fetch_add(1);
+  }
+  set_algo(c0, "p2p_batch");
+  return NBD_OK;
+}
 
 // ---------------------------------------------------------------------------
 // nbd_local_all_reduce_noalloc — all-reduce of R buffers on ONE GPU without any allocation

@@ -14,7 +14,7 @@
 //   warp 1       OUT  waits B(i) of every rank, staging slot -> user recv (TMA ring)
 //
 // Tile i of CTA b covers message units [(i*G + b)*Tu, +Tu) (G = grid size, Tu = tile units) and
-// lives in slot i % kPipeDepth of CTA b's part of the staging.  The transport of RED is a
+// lives in slot i % depth of CTA b's part of the staging.  The transport of RED is a
 // template switch:
 //   MC = true   NVSwitch multicast: multimem.ld_reduce (the switch fetches and sums the N
 //               copies) + multimem.st (the switch writes all N copies).  Wire bytes per GPU
@@ -26,7 +26,7 @@
 //
 // Flags are the arena's monotonic u64 clocks: A(i) and B(i) both carry the
 // value epoch+1+i, A in flag row b, B in flag row kPipeRowB + b, word = source rank.  A slot is
-// reused for tile i+kPipeDepth only after OUT has finished tile i, which (through B(i)) implies
+// reused for tile i+depth only after OUT has finished tile i, which (through B(i)) implies
 // that every rank has finished reading and writing that slot on every rank.
 //
 // No counterpart in the reference; semantics are those of dist.all_reduce / dist.broadcast as
@@ -37,12 +37,12 @@
 
 namespace nbd {
 
-constexpr int kPipeDepth = 3;                       // staging slots per CTA
+constexpr int kPipeDepth = 4;                       // default staging slots per CTA (OpParams::depth)
 constexpr int kPipeRowB = 256;                      // B flags live in rows [256, 256 + grid)
 constexpr int kPipeMaxBlocks = 256;                 // rows 512.. hold export slots
 constexpr int kPipeRedThreads = kThreads - 64;      // warps 2..15
 constexpr u32 kTmaPiece = 8192;                     // bytes per bulk copy
-constexpr int kTmaStages = 4;                       // bulk copies in flight per ring
+constexpr int kTmaStages = 12;                      // bulk copies in flight per ring (96 KiB)
 constexpr size_t kPipeSmemBytes = 2 * (size_t)kTmaStages * kTmaPiece;  // IN ring + OUT ring
 
 struct PipeBufs {
@@ -195,6 +195,7 @@ struct PipeGeom {
   u64 units;   // 16-byte units of the message
   u64 tu;      // units per tile
   u32 rounds;  // tiles per CTA
+  u32 depth;   // staging slots per CTA
 };
 
 __device__ __forceinline__ u64 tile_first(const PipeGeom& g, u32 i) { return ((u64)i * gridDim.x + blockIdx.x) * g.tu; }
@@ -203,7 +204,7 @@ __device__ __forceinline__ u64 tile_units(const PipeGeom& g, u32 i) {
   return f >= g.units ? 0 : (g.units - f < g.tu ? g.units - f : g.tu);
 }
 __device__ __forceinline__ u64 slot_offset(const PipeGeom& g, u32 i) {
-  return ((u64)blockIdx.x * kPipeDepth + (i % kPipeDepth)) * g.tu * kUnit;
+  return ((u64)blockIdx.x * g.depth + (i % g.depth)) * g.tu * kUnit;
 }
 
 // Staging hand-over with the neighbouring kernels of the stream.  The chunked kernels of
@@ -244,13 +245,13 @@ __device__ __forceinline__ void warp_tile_copy(TmaRing& R, const Region& user, u
 
 // reduce_loop_u of nbd_kernels.cuh for the reducing warps only (thread rt of kPipeRedThreads)
 template <typename T, bool SUM, int U, typename Src, typename Dst>
-__device__ __forceinline__ void pipe_reduce_loop(int N, u64 lo, u64 hi, int rt, int op, int avg, Src src, Dst dst) {
+__device__ __forceinline__ void pipe_reduce_loop(int N, u64 lo, u64 hi, int rt, int nthr, int op, int avg, Src src, Dst dst) {
   constexpr int KMAX = kMaxRanks / U;
-  for (u64 base = lo + rt; base < hi; base += (u64)U * kPipeRedThreads) {
+  for (u64 base = lo + rt; base < hi; base += (u64)U * nthr) {
     uint4 v[U][KMAX];
 #pragma unroll
     for (int j = 0; j < U; ++j) {
-      const u64 i = base + (u64)j * kPipeRedThreads;
+      const u64 i = base + (u64)j * nthr;
       if (i < hi) {
 #pragma unroll
         for (int k = 0; k < KMAX; ++k)
@@ -259,7 +260,7 @@ __device__ __forceinline__ void pipe_reduce_loop(int N, u64 lo, u64 hi, int rt, 
     }
 #pragma unroll
     for (int j = 0; j < U; ++j) {
-      const u64 i = base + (u64)j * kPipeRedThreads;
+      const u64 i = base + (u64)j * nthr;
       if (i < hi) {
         Reducer<T> R;
         R.init(v[j][0]);
@@ -268,6 +269,24 @@ __device__ __forceinline__ void pipe_reduce_loop(int N, u64 lo, u64 hi, int rt, 
           if (k < N) R.template add<SUM>(v[j][k], op);
         dst(i, R.result(avg, N));
       }
+    }
+  }
+}
+
+// In-switch reduction of units [lo, hi) of a slot: U loads in flight per thread, then U stores.
+template <typename T, int U>
+__device__ __forceinline__ void mc_reduce_loop(char* base, u64 lo, u64 hi, int gt, int nthr, int avg, int world) {
+  for (u64 b0 = lo + gt; b0 < hi; b0 += (u64)U * nthr) {
+    uint4 v[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 u = b0 + (u64)j * nthr;
+      if (u < hi) v[j] = McSum<T>::ld(base + u * kUnit);
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const u64 u = b0 + (u64)j * nthr;
+      if (u < hi) mc_st(base + u * kUnit, avg ? unit_div<T>(v[j], world) : v[j]);
     }
   }
 }
@@ -282,6 +301,7 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
   extern __shared__ __align__(128) unsigned char pipe_smem[];
   __shared__ uint64_t bars[2 * kTmaStages];
   __shared__ volatile u32 out_done;  // tiles this CTA's OUT warp has finished
+  __shared__ volatile u32 b_next;    // next tile whose B flag may be written (keeps the two RED groups in order)
 
   const int ci = ctx_index<NCTX>();
   const RankCtx& c = pk.ctx[ci];
@@ -293,12 +313,14 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
   g.units = units_of(op.bytes);
   g.tu = op.chunk_bytes / kUnit;
   g.rounds = op.nchunks;
+  g.depth = (u32)op.depth;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const u64 rowA = (u64)blockIdx.x * kMaxRanks, rowB = (u64)(kPipeRowB + blockIdx.x) * kMaxRanks;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2 * kTmaStages; ++s) mbar_init(&bars[s], 1);
     out_done = 0;
+    b_next = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   const u64 E = pipe_open(c, clk, op);
@@ -308,9 +330,9 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
     TmaRing R = {pipe_smem, bars, 0};
     const Region src = make_region(ub.send, op.bytes);
     for (u32 i = 0; i < g.rounds; ++i) {
-      if (i >= (u32)kPipeDepth) {
+      if (i >= g.depth) {
         if (lane == 0) {
-          while (out_done < i - kPipeDepth + 1) {
+          while (out_done < i - g.depth + 1) {
           }
         }
         __syncwarp();
@@ -344,10 +366,15 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
     }
   } else {
     // ---------------- RED: wait A(i), reduce own sub-shard, write it everywhere, signal B(i) ----
+    // op.algo bit 1: the 14 warps work as TWO groups on alternate tiles, so that one group's
+    // drain (the release before B(i) waits for its multicast stores) overlaps the other's loads.
+    const int ngroups = (op.algo & 2) ? 2 : 1;
+    const int nthr = kPipeRedThreads / ngroups;
     const int rt = threadIdx.x - 64;
-    for (u32 i = 0; i < g.rounds; ++i) {
-      if (rt < N) wait_flag(c, c.flags[r] + rowA + rt, E + 1 + i);
-      named_bar_sync(1, kPipeRedThreads);
+    const int grp = rt / nthr, gt = rt - grp * nthr;
+    for (u32 i = (u32)grp; i < g.rounds; i += (u32)ngroups) {
+      if (gt < N) wait_flag(c, c.flags[r] + rowA + gt, E + 1 + i);
+      named_bar_sync(1 + grp, nthr);
       const u64 tu = tile_units(g, i);
       const u64 su = (tu + N - 1) / N;
       u64 lo = (u64)r * su;
@@ -356,20 +383,8 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
       if (hi > tu) hi = tu;
       const u64 soff = slot_offset(g, i);
       if (MC) {
-        char* base = pb.mc + soff;
-        for (u64 b0 = lo + rt; b0 < hi; b0 += 4ull * kPipeRedThreads) {
-          uint4 v[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const u64 u = b0 + (u64)j * kPipeRedThreads;
-            if (u < hi) v[j] = McSum<T>::ld(base + u * kUnit);
-          }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const u64 u = b0 + (u64)j * kPipeRedThreads;
-            if (u < hi) mc_st(base + u * kUnit, op.avg ? unit_div<T>(v[j], N) : v[j]);
-          }
-        }
+        if (op.algo & 4) mc_reduce_loop<T, 8>(pb.mc + soff, lo, hi, gt, nthr, op.avg, N);
+        else mc_reduce_loop<T, 4>(pb.mc + soff, lo, hi, gt, nthr, op.avg, N);
       } else {
         // peer-to-peer transport: ascending-rank reduction of the N staged copies, result
         // written into every rank's slot (own first, then rotated); few ranks -> deeper unroll
@@ -385,12 +400,22 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
             }
           }
         };
-        if (N <= 2) pipe_reduce_loop<T, SUM, 4>(N, lo, hi, rt, op.op, op.avg, src, dst);
-        else if (N <= 4) pipe_reduce_loop<T, SUM, 2>(N, lo, hi, rt, op.op, op.avg, src, dst);
-        else pipe_reduce_loop<T, SUM, 1>(N, lo, hi, rt, op.op, op.avg, src, dst);
+        if (N <= 2) pipe_reduce_loop<T, SUM, 4>(N, lo, hi, gt, nthr, op.op, op.avg, src, dst);
+        else if (N <= 4) pipe_reduce_loop<T, SUM, 2>(N, lo, hi, gt, nthr, op.op, op.avg, src, dst);
+        else pipe_reduce_loop<T, SUM, 1>(N, lo, hi, gt, nthr, op.op, op.avg, src, dst);
       }
-      named_bar_sync(1, kPipeRedThreads);
-      if (rt < N) st_release_sys(c.flags[rt] + rowB + r, E + 1 + i);
+      named_bar_sync(1 + grp, nthr);
+      if (gt < N) {
+        // flags only grow and B(i) must imply B(i-1): the two groups signal in tile order
+        while (b_next != i) {
+        }
+        st_release_sys(c.flags[gt] + rowB + r, E + 1 + i);
+        __syncwarp((1u << N) - 1u);
+        if (gt == 0) {
+          __threadfence_block();
+          b_next = i + 1;
+        }
+      }
     }
   }
   pipe_close(c, E, g.rounds, op);
@@ -418,6 +443,7 @@ k_broadcast_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
   g.units = units_of(op.bytes);
   g.tu = op.chunk_bytes / kUnit;
   g.rounds = op.nchunks;
+  g.depth = (u32)op.depth;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const u64 rowA = (u64)blockIdx.x * kMaxRanks, rowB = (u64)(kPipeRowB + blockIdx.x) * kMaxRanks;
 
@@ -433,8 +459,8 @@ k_broadcast_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
       const Region src = make_region(ub.recv, op.bytes);
       const bool al = region_aligned(src);
       for (u32 i = 0; i < g.rounds; ++i) {
-        if (i >= (u32)kPipeDepth) {  // every reader has copied tile i - depth out of this slot
-          if (rt < N && rt != r) wait_flag(c, c.flags[r] + rowB + rt, E + 1 + (i - kPipeDepth));
+        if (i >= g.depth) {  // every reader has copied tile i - depth out of this slot
+          if (rt < N && rt != r) wait_flag(c, c.flags[r] + rowB + rt, E + 1 + (i - g.depth));
           named_bar_sync(1, kPipeRedThreads);
         }
         const u64 tu = tile_units(g, i), first = tile_first(g, i), soff = slot_offset(g, i);

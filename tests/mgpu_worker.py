@@ -99,6 +99,7 @@ def body(rank: int, world: int, port: int) -> None:
         assert nv_on, f"multicast expected on this box: {nv_why}"
     if nv_on:
         be.set_tunable("nvls_min_bytes", 1)
+        be.set_tunable("nvls_bcast", 1)  # off by default: the scatter kernel is faster
         for nbytes in (40, (48 << 10) + 5, (1 << 20) + 17, (9 << 20) + 1):
             for root in sorted({0, world - 1}):
                 x = O.make_inputs(world, nbytes, "u8", seed=70 + root)
@@ -111,7 +112,16 @@ def body(rank: int, world: int, port: int) -> None:
         v.copy_(H.to_cuda(x[rank], "u8", dev))
         dist.broadcast(v, src=1 % world)
         H.assert_same(_np(v, "u8"), x[1 % world], "u8", "multicast broadcast into a misaligned view")
+        be.set_tunable("nvls_bcast", 0)
         be.set_tunable("nvls_reduce", 1)
+        for mode in (0, 2, 6):  # one / two reducing groups, 4 / 8 loads in flight
+            be.set_tunable("pipe_mode", mode)
+            xi = [np.random.default_rng(60 + r).integers(-1000, 1000, (2 << 20) + 11).astype(np.float32) for r in range(world)]
+            t = H.to_cuda(xi[rank], "f32", dev)
+            dist.all_reduce(t)
+            assert be.last_algo() == "ar_nvls"
+            H.assert_same(_np(t, "f32"), O.reduce_rank_order(xi, "f32"), "f32", f"in-switch sum, pipe_mode {mode}")
+        be.set_tunable("pipe_mode", 0)
         for dtype in ("f32", "bf16", "f16"):
             for numel in (4099, (1 << 20) + 1, (5 << 20) + 3):
                 x = O.make_inputs(world, numel, dtype, seed=80)

@@ -100,6 +100,36 @@ def test_pipe_many_rounds_reuse_slots(torch_cuda, groups, world, tile):
         grp.set_tunable("blocks", 0)
 
 
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("depth", [2, 3, 4])
+@pytest.mark.parametrize("mode", [0, 2])
+def test_pipe_shapes_slots_and_reducing_groups(torch_cuda, groups, world, depth, mode):
+    """Every pipeline shape the planner can be tuned to: 2-4 slots per CTA, one or two groups
+    of reducing warps (mode bit 1; the groups take alternate tiles and must still signal in tile
+    order), many short rounds."""
+    grp = groups(world)
+    knobs = {"pipe_depth": depth, "pipe_mode": mode, "pipe_tile_bytes": 8192, "blocks": 4}
+    for k, v in knobs.items():
+        grp.set_tunable(k, v)
+    try:
+        for dtype, numel in (("bf16", (1 << 20) + 9), ("f32", 300_001)):
+            x = O.make_inputs(world, numel, dtype, seed=7)
+            got, _ = _all_reduce(torch_cuda, grp, x, dtype)
+            want = O.reduce_rank_order(x, dtype)
+            for r in range(world):
+                H.assert_same(got[r], want, dtype, f"{dtype} rank {r}")
+        x = O.make_inputs(world, (1 << 20) + 3, "u8", seed=8)
+        t = [H.to_cuda(a, "u8") for a in x]
+        grp.broadcast(t, root=world - 1)
+        torch_cuda.cuda.synchronize()
+        grp.async_error()
+        for r in range(world):
+            H.assert_same(H.to_numpy(t[r], "u8"), x[world - 1], "u8", f"broadcast rank {r}")
+    finally:
+        for k in knobs:
+            grp.set_tunable(k, 0)
+
+
 @pytest.mark.parametrize("world", [2, 4])
 @pytest.mark.parametrize("offset", [1, 2, 4, 8])
 def test_pipe_misaligned_views(torch_cuda, groups, world, offset):

@@ -40,6 +40,7 @@ def main():
         if rank == 0:
             print(json.dumps(obj), flush=True)
 
+    nvls_only = "--nvls" in sys.argv
     warm = torch.zeros(1024, device=dev)
     dist.all_reduce(warm)  # creates the communicator (and the multicast object)
     torch.cuda.synchronize()
@@ -80,6 +81,45 @@ def main():
     big = torch.empty((1 << 30) // 4, device=dev, dtype=torch.float32)
     g = torch.Generator(device=dev)
     g.manual_seed(1234 + rank)
+    f_ar = 2.0 * (world - 1) / world
+    if nvls_only:
+        # in-switch all_reduce: pipeline shape sweep (tile bytes, slots, reducing groups, loads in flight)
+        for nbytes in (64 << 20, 256 << 20):
+            n = nbytes // 4
+            x = big[:n]
+            src = torch.randint(-1000, 1000, (n,), generator=g, device=dev, dtype=torch.int32)
+            want = src.clone()
+            dist.all_reduce(want)
+            want = want.to(torch.float32)
+            per4 = -(-nbytes // (148 * 4) // 128) * 128
+            per2 = -(-nbytes // (148 * 2) // 128) * 128
+            per8 = -(-nbytes // (148 * 8) // 128) * 128
+            for tile in (per8, 256 << 10 if nbytes > (64 << 20) else per4, per4, per2):
+                for depth in (3, 4):
+                    for mode in (0, 2, 4, 6):
+                        kv = {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "pipe_depth": depth, "pipe_mode": mode}
+                        with knobs(**kv):
+                            x.copy_(src)
+                            dist.all_reduce(x)
+                            ok = bool(torch.equal(x, want))
+                            algo = be.last_algo()
+                            x.zero_()
+                            us = timed(lambda: dist.all_reduce(x), 10)
+                        emit({"op": "all_reduce", "variant": f"nvls/tile={tile}/depth={depth}/mode={mode}", "bytes": nbytes,
+                              "us": round(us, 2), "busbw": round(nbytes * f_ar / us / 1e3, 1), "algo": algo, "ok": ok})
+            with knobs(auto_min_bytes=1 << 20, pipe=2, nvls_off=1):
+                for _ in range(3):
+                    dist.all_reduce(x)
+                us = timed(lambda: dist.all_reduce(x), 10)
+            emit({"op": "all_reduce", "variant": "auto", "bytes": nbytes, "us": round(us, 2), "busbw": round(nbytes * f_ar / us / 1e3, 1)})
+            if nccl is not None:
+                us = timed(lambda: dist.all_reduce(x, group=nccl), 10)
+                emit({"op": "all_reduce", "variant": "nccl", "bytes": nbytes, "us": round(us, 2), "busbw": round(nbytes * f_ar / us / 1e3, 1)})
+            del src, want
+        dist.barrier(group=cpu)
+        del big
+        W.shutdown_worker()
+        return
     sizes = [1 << 20, 4 << 20, 16 << 20, 64 << 20, 256 << 20] + ([] if quick else [1 << 30])
     f_ar = 2.0 * (world - 1) / world
 

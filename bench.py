@@ -88,7 +88,7 @@ class ClockSampler:
         0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
     }
 
-    def __init__(self, device_index: int = 0, period_s: float = 0.002):
+    def __init__(self, device_index: int = 0, period_s: float = 0.005):
         self.device_index = device_index
         self.period_s = period_s
         self.samples = []
@@ -586,21 +586,29 @@ def run_ours_multi(args):
     l0 = B.launch_count()
     torch.cuda.synchronize()
     dist.barrier(group=cpu_group)
-    nvl0 = nvlink_bytes(physical_gpu_index(local)) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
     torch.cuda.synchronize()
-    nvl1 = nvlink_bytes(physical_gpu_index(local)) if rank == 0 else None
     dist.barrier(group=cpu_group)
     launches = B.launch_count() - l0
-    nvlink = None
-    if nvl0 and nvl1:
-        nvlink = {"tx_bytes_per_step": (nvl1[0] - nvl0[0]) / args.steps, "rx_bytes_per_step": (nvl1[1] - nvl0[1]) / args.steps,
-                  "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX of rank 0's GPU, all links, over the timed region / steps"}
     clocks = sampler.stop() if sampler else None
+    sampler = None
+    # NVLink payload bytes of the same step, counted in a SEPARATE untimed pass (NVML queries
+    # stay out of the timed region)
+    nvlink = None
+    nvl0 = nvlink_bytes(physical_gpu_index(local)) if rank == 0 else None
+    dist.barrier(group=cpu_group)
+    for _ in range(5):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier(group=cpu_group)
+    nvl1 = nvlink_bytes(physical_gpu_index(local)) if rank == 0 else None
+    if nvl0 and nvl1:
+        nvlink = {"tx_bytes_per_step": (nvl1[0] - nvl0[0]) / 5, "rx_bytes_per_step": (nvl1[1] - nvl0[1]) / 5,
+                  "source": "NVML NVLINK_THROUGHPUT_DATA_TX/RX of rank 0's GPU, all links, over 5 untimed repeats of the step"}
     t = torch.tensor([e0.elapsed_time(e1) / args.steps], dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
     ms = float(t.item())

@@ -67,6 +67,12 @@ struct RankCtx {
 constexpr u64 kLLMaxBytes = 32ull << 10;
 constexpr u64 kLLSlotBytes = 2 * kLLMaxBytes;
 constexpr u64 kLLAreaBytes = 2 * (u64)kMaxRanks * kLLSlotBytes;  // 1 MiB
+// Row of the flag array where rank `src` publishes "LL operations I have finished reading" (word
+// = src).  A rank that WRITES packets for LL operation s first checks that every receiver has
+// finished operation s-2, the previous user of the same parity buffer: with all_reduce alone
+// that is implied (one cannot get two operations ahead of a peer whose packets one needs), but
+// the root of an LL broadcast needs nothing from its peers and could otherwise lap them.
+constexpr int kLLAckRow = 480;
 
 struct RankBufs {
   const char* send;

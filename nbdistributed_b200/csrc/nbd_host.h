@@ -73,7 +73,14 @@ struct NvlsState {
   bool enabled = false;     // set only when every rank of the communicator finished the set-up
   int listen_fd = -1;       // rank 0: the socket its peers connect to during nbd_comm_connect
   uint64_t nonce = 0;       // names that socket (abstract unix namespace); 0 = multicast not wanted
-  size_t bytes = 0;         // staging bytes per rank
+  size_t bytes = 0;         // bytes bound into the multicast object per rank: staging, then the symmetric pool
+  size_t stage_bytes = 0;   // [0, stage_bytes): staging of the tile-pipeline kernels
+  size_t pool_bytes = 0;    // [stage_bytes, +pool_bytes): symmetric memory handed out by nbd_mem_alloc
+  struct PoolBlock {
+    size_t off, len;
+    bool used;
+  };
+  std::vector<PoolBlock> pool;  // address-ordered blocks of the symmetric pool
   size_t granularity = 0;
   unsigned long long mem = 0, mc = 0;  // CUmemGenericAllocationHandle of the staging / the multicast object
   bool have_mem = false, have_mc = false, added = false, bound = false;
@@ -103,6 +110,7 @@ struct nbd_comm {
     size_t bytes = 0;
     void* peer[kMaxRanks] = {};
     bool connected = false;
+    char* mc = nullptr;                 // multicast alias (memory from the NVSwitch-multicast pool): multimem.* only
   };
   std::vector<Registration> regs;
   // auto-registration of ordinary allocations (exports: ours; imports: peers')
@@ -139,6 +147,8 @@ struct nbd_comm {
 int nvls_prepare(nbd_comm* c);                       // nbd_comm_create: rank 0 opens the rendezvous socket
 void nvls_setup(nbd_comm* c, uint64_t nonce_rank0);  // nbd_comm_connect: collective; leaves nvls.enabled
 void nvls_teardown(nbd_comm* c);
+char* nvls_pool_alloc(nbd_comm* c, size_t bytes, char** mc_alias);  // nullptr: pool absent or exhausted
+bool nvls_pool_free(nbd_comm* c, char* ptr);                        // false: not a pool pointer
 
 struct EmuGroup {
   int world = 0;

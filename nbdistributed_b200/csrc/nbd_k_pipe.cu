@@ -43,4 +43,13 @@ const void* pipe_broadcast_kernel(bool emu, bool mc) {
 }
 
 size_t pipe_smem_bytes() { return kPipeSmemBytes; }
+
+const void* mcz_allreduce_kernel(int dtype) {
+  switch (dtype) {
+    case NBD_F32: return (const void*)k_allreduce_mcz<float>;
+    case NBD_BF16: return (const void*)k_allreduce_mcz<__nv_bfloat16>;
+    case NBD_F16: return (const void*)k_allreduce_mcz<__half>;
+    default: return nullptr;
+  }
+}
 }  // namespace nbd

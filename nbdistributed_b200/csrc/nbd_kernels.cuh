@@ -194,6 +194,30 @@ __device__ __forceinline__ uint4 ld_ll(const char* p) {
   return v;
 }
 
+// Before writing packets of LL operation `seq`: every receiver has finished operation seq - 2.
+__device__ __forceinline__ void ll_wait_acks(const RankCtx& c, u64 seq) {
+  const int t = threadIdx.x;
+  if (seq >= 2 && t < c.world && t != c.rank) wait_flag(c, c.flags[c.rank] + (u64)kLLAckRow * kMaxRanks + t, seq - 1);
+  __syncthreads();
+}
+
+// End of an LL operation: the last CTA of this rank advances the LL clock and tells every peer
+// that this rank has finished reading operation `seq`.
+__device__ __forceinline__ void ll_finish(const RankCtx& c, u64 seq) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    LocalState* s = c.state;
+    const u32 prev = atomicAdd(&s->done, 1u);
+    if (prev == gridDim.x - 1) {
+      s->done = 0;
+      s->ll_seq = seq + 1;
+      __threadfence();
+      for (int p = 0; p < c.world; ++p)
+        if (p != c.rank) *reinterpret_cast<volatile u64*>(c.flags[p] + (u64)kLLAckRow * kMaxRanks + c.rank) = seq + 1;
+    }
+  }
+}
+
 template <typename T, bool SUM, int NCTX>
 __global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
 k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
@@ -211,6 +235,7 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   u64 lo, hi;
   block_span(units, units, lo, hi);
   char* my_ll = c.stage[r] + c.ll_off + par;
+  ll_wait_acks(c, seq);
   for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
     uint4 v[kMaxRanks];
     const uint4 mine = region_ld(src, als, i);
@@ -258,16 +283,66 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
       if (k < N) R.template add<SUM>(v[k], op.op);
     region_st(dst, ald, i, R.result(op.avg, N));
   }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    LocalState* s = c.state;
-    const u32 prev = atomicAdd(&s->done, 1u);
-    if (prev == gridDim.x - 1) {
-      s->done = 0;
-      s->ll_seq = seq + 1;
-      __threadfence();
+  ll_finish(c, seq);
+}
+
+// broadcast, LL (<= kLLMaxBytes): the root writes {data, flag} packets into its slot of every
+// peer's LL area, the peers spin on the packets and copy them out.  No barrier, no fence.
+template <int NCTX>
+__global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
+k_broadcast_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
+  const int ci = ctx_index<NCTX>();
+  const RankCtx& c = pk.ctx[ci];
+  const RankBufs& ub = pk.buf[ci];
+  const int N = c.world, r = c.rank, root = op.root;
+  const volatile LocalState* st = c.state;
+  const u64 seq = st->ll_seq;
+  const u32 flag = (u32)(seq % 0xfffffffeull) + 1u;
+  const u64 par = (seq & 1) * (u64)kMaxRanks * kLLSlotBytes;
+  const Region buf = make_region(ub.recv, op.bytes);
+  const bool al = region_aligned(buf);
+  const u64 units = units_of(op.bytes);
+  u64 lo, hi;
+  block_span(units, units, lo, hi);
+  if (r == root) {
+    ll_wait_acks(c, seq);
+    for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
+      const uint4 mine = region_ld(buf, al, i);
+#pragma unroll
+      for (int k = 1; k < kMaxRanks; ++k) {
+        if (k < N) {
+          int p = r + k;
+          if (p >= N) p -= N;
+          char* d = c.stage[p] + c.ll_off + par + (u64)r * kLLSlotBytes + i * 32;
+          st_ll(d, mine.x, mine.y, flag);
+          st_ll(d + 16, mine.z, mine.w, flag);
+        }
+      }
+    }
+  } else {
+    const char* slot = c.stage[r] + c.ll_off + par + (u64)root * kLLSlotBytes;
+    for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
+      const char* s = slot + i * 32;
+      uint4 a = ld_ll(s), b = ld_ll(s + 16);
+      u32 spins = 0;
+      u64 t0 = 0;
+      while (a.y != flag || a.w != flag || b.y != flag || b.w != flag) {
+        a = ld_ll(s);
+        b = ld_ll(s + 16);
+        if ((++spins & 0xFFFFu) == 0) {  // watchdog, as in wait_flag_slow
+          const u64 now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          volatile HostMailbox* mb = c.mbox;
+          volatile LocalState* ls = c.state;
+          if (mb->abort) { mb->error = 5; ls->failed = 1; break; }
+          if (c.timeout_ns != 0 && now - t0 > c.timeout_ns) { mb->error = 4; ls->failed = 1; break; }
+          if (ls->failed != 0) break;
+        }
+      }
+      region_st(buf, al, i, make_uint4(a.x, a.z, b.x, b.z));
     }
   }
+  ll_finish(c, seq);
 }
 
 // ---------------------------------------------------------------------------

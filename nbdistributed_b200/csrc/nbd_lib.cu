@@ -157,7 +157,7 @@ static void free_rank(nbd_comm* c) {
     if (!c->emu)
       for (int p = 0; p < c->world; ++p)
         if (p != c->rank && g.peer[p]) cudaIpcCloseMemHandle(g.peer[p]);
-    if (g.base) cudaFree(g.base);
+    if (g.base && !g.mc) cudaFree(g.base);
   }
   c->regs.clear();
   for (void* m : c->import_ptrs) cudaIpcCloseMemHandle(m);
@@ -584,6 +584,19 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
   p.op.bytes = bytes;
   p.op.root = root;
   p.op.world = N;
+  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kLLMaxBytes;
+  if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= kLLMaxBytes) {
+    p.op.algo = 2;  // LL: packets carry their own flags, no barrier (4 KiB: ~half the latency of "direct")
+    p.op.chunk_bytes = bytes;
+    p.op.nchunks = 1;
+    u64 want = ceil_div(ceil_div(bytes, kUnit), (u64)kThreads);
+    u64 cap = emu_world > 1 ? (u64)c->num_sms / emu_world : 8;
+    if (cap > 8) cap = 8;
+    if (cap < 1) cap = 1;
+    p.nblocks = (int)(want < 1 ? 1 : (want < cap ? want : cap));
+    c->last_algo = "bcast_ll";
+    return p;
+  }
   if (bytes <= direct_max) {
     p.op.algo = 0;
     u64 cap = floor_to(half, kUnit);
@@ -645,7 +658,7 @@ static int plan_pipe(nbd_comm* c, u64 bytes, u64 capacity, int emu_world, Plan* 
   p.op.nchunks = (u32)ceil_div(ceil_div(bytes, kUnit) * kUnit, G * tile);
   p.op.world = c->world;
   p.op.depth = (int)depth;
-  p.op.algo = (int)(c->t_pipe_mode & 6);  // callers add bit 0 (open with a barrier) for arena staging
+  p.op.algo = (int)(c->t_pipe_mode & 62);  // bits 3-5: timing diagnostics (skip copy-in / copy-out / reduction)  // callers add bit 0 (open with a barrier) for arena staging
   p.nblocks = (int)G;
   *out = p;
   return NBD_OK;
@@ -710,7 +723,7 @@ static int pipe_all_reduce(nbd_comm* c, const void* send, void* recv, u64 bytes,
   const void* fn = pipe_allreduce_kernel(dtype, sum, false, mc);
   if (!fn) return fail(NBD_ERR_UNSUPPORTED, "dtype %d / op %d has no tile-pipeline kernel", dtype, op);
   Plan p;
-  int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.bytes : 2 * c->ctx.half_bytes, 0, &p);
+  int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.stage_bytes : 2 * c->ctx.half_bytes, 0, &p);
   if (rc != NBD_OK) return rc;
   p.op.op = op;
   p.op.avg = (op == NBD_AVG);
@@ -724,7 +737,7 @@ static int pipe_all_reduce(nbd_comm* c, const void* send, void* recv, u64 bytes,
 static int pipe_broadcast(nbd_comm* c, void* buf, u64 bytes, int root, bool mc, cudaStream_t s) {
   const void* fn = pipe_broadcast_kernel(false, mc);
   Plan p;
-  int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.bytes : 2 * c->ctx.half_bytes, 0, &p);
+  int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.stage_bytes : 2 * c->ctx.half_bytes, 0, &p);
   if (rc != NBD_OK) return rc;
   p.op.root = root;
   p.op.algo |= mc ? 0 : 1;
@@ -826,7 +839,20 @@ static int find_reg(const nbd_comm* c, const void* ptr, u64 bytes, u64* off) {
   const char* p = static_cast<const char*>(ptr);
   for (size_t k = 0; k < c->regs.size(); ++k) {
     const auto& g = c->regs[k];
-    if (g.connected && g.base && p >= g.base && p + bytes <= g.base + g.bytes) {
+    if (g.connected && g.base && !g.mc && p >= g.base && p + bytes <= g.base + g.bytes) {
+      *off = (u64)(p - g.base);
+      return (int)k;
+    }
+  }
+  return -1;
+}
+
+// multicast-pool registration (nbd_mem_alloc with in-switch reduction on) that contains [ptr, ptr+bytes), or -1
+static int find_mc_reg(const nbd_comm* c, const void* ptr, u64 bytes, u64* off) {
+  const char* p = static_cast<const char*>(ptr);
+  for (size_t k = 0; k < c->regs.size(); ++k) {
+    const auto& g = c->regs[k];
+    if (g.base && g.mc && p >= g.base && p + bytes <= g.base + g.bytes) {
       *off = (u64)(p - g.base);
       return (int)k;
     }
@@ -1072,7 +1098,26 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
                                  &prm);
     }
   }
-  if (nvls_reduce_wanted(c, bytes, dtype, op)) return pipe_all_reduce(c, send, recv, bytes, dtype, op, true, s);
+  if (nvls_reduce_wanted(c, bytes, dtype, op)) {
+    // both buffers in the multicast pool, whole 16-byte units: no staging, the switch does it all
+    u64 offs = 0, offr = 0;
+    const int ks = (bytes % kUnit == 0) ? find_mc_reg(c, send, bytes, &offs) : -1;
+    const int kr = ks >= 0 ? find_mc_reg(c, recv, bytes, &offr) : -1;
+    const void* fn = (ks >= 0 && kr >= 0 && offs % kUnit == 0 && offr % kUnit == 0) ? mcz_allreduce_kernel(dtype) : nullptr;
+    if (fn) {
+      Pack<1> pk;
+      fill_pack(pk, c, send, recv);
+      McPtrs m = {c->regs[ks].mc + offs, c->regs[kr].mc + offr};
+      OpParams prm = zc_params(c, bytes, op, 0);
+      const int nb = pick_blocks(c, ceil_div(bytes / kUnit, (u64)c->world), 0);
+      void* args[3] = {(void*)&pk, (void*)&m, (void*)&prm};
+      NBD_CUDA(cudaLaunchKernel(fn, dim3(nb, 1, 1), dim3(kThreads, 1, 1), args, 0, s));
+      g_launches.fetch_add(1);
+      c->last_algo = "ar_nvls_zerocopy";
+      return NBD_OK;
+    }
+    return pipe_all_reduce(c, send, recv, bytes, dtype, op, true, s);
+  }
   if (pipe_wanted(c, bytes)) return pipe_all_reduce(c, send, recv, bytes, dtype, op, false, s);
   if (auto_wanted_ar(c, bytes)) {
     // ordinary tensors: agree on the device whether every rank can address every rank's
@@ -1244,7 +1289,7 @@ int nbd_broadcast(nbd_comm_t c, void* buf, size_t count, int dtype, int root, vo
   Plan p = plan_broadcast(c, (u64)count * es, root, 0);
   Pack<1> pk;
   fill_pack(pk, c, buf, buf);
-  return launch_any<1>((const void*)k_broadcast<1>, p.nblocks, 1, s, pk, &p.op);
+  return launch_any<1>(p.op.algo == 2 ? (const void*)k_broadcast_ll<1> : (const void*)k_broadcast<1>, p.nblocks, 1, s, pk, &p.op);
 }
 
 int nbd_barrier(nbd_comm_t c, void* stream) {
@@ -1418,8 +1463,9 @@ int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count, int dtype
   Pack<kMaxRanks> pk;
   if ((rc = fill_pack_emu(pk, g, (const void* const*)bufs, bufs)) != NBD_OK) return rc;
   Plan p = plan_broadcast(c0, (u64)count * es, root, g->world);
-  return launch_any<kMaxRanks>((const void*)k_broadcast<kMaxRanks>, p.nblocks, g->world, (cudaStream_t)stream, pk,
-                               &p.op);
+  for (int r = 1; r < g->world; ++r) g->comms[r]->last_algo = c0->last_algo;
+  return launch_any<kMaxRanks>(p.op.algo == 2 ? (const void*)k_broadcast_ll<kMaxRanks> : (const void*)k_broadcast<kMaxRanks>,
+                               p.nblocks, g->world, (cudaStream_t)stream, pk, &p.op);
 }
 
 int nbd_emu_barrier(nbd_comm_t any, void* stream) {
@@ -1852,6 +1898,37 @@ extern "C" int nbd_mem_alloc(nbd_comm_t c, size_t bytes, void** ptr, void* handl
   if (bytes == 0) return fail(NBD_ERR_INVALID_ARGUMENT, "cannot allocate 0 bytes");
   DeviceGuard g(c->device);
   const size_t rounded = (bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
+  if (c->nvls.enabled && c->t_nvls_reduce && !c->t_nvls_off) {
+    // In-switch reduction is on: hand out memory that is bound into the multicast object, so
+    // that all_reduce on it needs no staging.  Peers do not map it (multimem.* reaches every
+    // copy through the switch); every other collective treats it as an ordinary buffer.
+    char* mc = nullptr;
+    char* p = nvls_pool_alloc(c, rounded, &mc);
+    if (p) {
+      Handle h;
+      memset(&h, 0, sizeof(h));
+      h.magic = kMagic;
+      h.version = NBD_VERSION;
+      h.rank = c->rank;
+      h.world = c->world;
+      h.pid = (int64_t)getpid();
+      h.hostid = host_id();
+      h.arena_bytes = rounded;
+      h.stage_bytes = (uint64_t)c->regs.size();
+      h.nvls_nonce = (uint64_t)(p - c->nvls.local) | (1ull << 63);  // pool offset: must match on every rank
+      nbd_comm::Registration reg;
+      reg.base = p;
+      reg.bytes = rounded;
+      reg.peer[c->rank] = p;
+      reg.mc = mc;
+      reg.connected = false;
+      c->regs.push_back(reg);
+      memset(handle_out, 0, NBD_HANDLE_BYTES);
+      memcpy(handle_out, &h, sizeof(h));
+      *ptr = p;
+      return NBD_OK;
+    }
+  }
   char* base = nullptr;
   NBD_CUDA(cudaMalloc((void**)&base, rounded));
   Handle h;
@@ -1892,6 +1969,19 @@ extern "C" int nbd_mem_connect(nbd_comm_t c, void* ptr, const void* all_handles)
   if (k < 0) return fail(NBD_ERR_INVALID_ARGUMENT, "pointer was not returned by nbd_mem_alloc on this communicator");
   auto& reg = c->regs[(size_t)k];
   if (reg.connected) return NBD_OK;
+  if (reg.mc) {  // multicast pool: nothing to map, only check that every rank got the same piece
+    const uint64_t mine = (uint64_t)(reg.base - c->nvls.local) | (1ull << 63);
+    for (int p = 0; p < c->world; ++p) {
+      Handle h;
+      memcpy(&h, (const char*)all_handles + (size_t)p * NBD_HANDLE_BYTES, sizeof(h));
+      if (h.magic != kMagic || h.rank != p || h.world != c->world) return fail(NBD_ERR_INVALID_ARGUMENT, "memory handle %d is malformed", p);
+      if (h.nvls_nonce != mine || h.arena_bytes != reg.bytes)
+        return fail(NBD_ERR_MISMATCH, "rank %d holds a different piece of the multicast pool: nbd_mem_alloc/free must be called in the "
+                    "same order with the same sizes on every rank", p);
+    }
+    reg.connected = true;
+    return NBD_OK;
+  }
   DeviceGuard g(c->device);
   for (int p = 0; p < c->world; ++p) {
     if (p == c->rank) continue;
@@ -1920,6 +2010,14 @@ extern "C" int nbd_mem_free(nbd_comm_t c, void* ptr) {
   DeviceGuard g(c->device);
   for (auto& reg : c->regs) {
     if (reg.base != ptr) continue;
+    if (reg.mc) {
+      nvls_pool_free(c, reg.base);
+      reg.base = nullptr;
+      reg.mc = nullptr;
+      reg.bytes = 0;
+      reg.connected = false;
+      return NBD_OK;
+    }
     for (int p = 0; p < c->world; ++p)
       if (p != c->rank && reg.peer[p]) {
         cudaIpcCloseMemHandle(reg.peer[p]);

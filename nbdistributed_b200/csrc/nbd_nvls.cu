@@ -237,12 +237,13 @@ bool env_off() {
   return e && e[0] == '0';
 }
 
-size_t wanted_bytes() {
-  const char* e = getenv("NBDIST_B200_NVLS_BYTES");
-  size_t v = e ? (size_t)strtoull(e, nullptr, 0) : 0;
-  if (v == 0) v = 128ull << 20;
-  return v;
+size_t env_bytes(const char* name, size_t dflt) {
+  const char* e = getenv(name);
+  if (!e) return dflt;
+  return (size_t)strtoull(e, nullptr, 0);
 }
+
+size_t round_up(size_t v, size_t g) { return (v + g - 1) / g * g; }
 
 // ---- the steps every rank performs locally ------------------------------------------------------
 struct Local {
@@ -263,13 +264,22 @@ bool step_alloc(nbd_comm* c, Local* L) {
   memset(&L->prop, 0, sizeof(L->prop));
   L->prop.numDevices = (unsigned)c->world;
   L->prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
-  L->prop.size = wanted_bytes();
+  L->prop.size = 128ull << 20;
   size_t gran = 0;
   r = d.MulticastGetGranularity(&gran, &L->prop, CU_MULTICAST_GRANULARITY_RECOMMENDED);
   if (r != CUDA_SUCCESS || gran == 0) return why(c, "cuMulticastGetGranularity: %s", cu_str(r)), false;
   NvlsState& s = c->nvls;
   s.granularity = gran;
-  s.bytes = (wanted_bytes() + gran - 1) / gran * gran;
+  // staging for the tile-pipeline kernels, then a pool that nbd_mem_alloc hands out as symmetric
+  // memory (zero-copy in-switch all_reduce); both in units of the recommended granularity
+  size_t stage = env_bytes("NBDIST_B200_NVLS_BYTES", 128ull << 20);
+  if (stage == 0) stage = 128ull << 20;
+  s.stage_bytes = round_up(stage, gran);
+  const size_t pool = env_bytes("NBDIST_B200_NVLS_POOL_BYTES", 1ull << 30);
+  s.pool_bytes = pool ? round_up(pool, gran) : 0;
+  s.bytes = s.stage_bytes + s.pool_bytes;
+  s.pool.clear();
+  if (s.pool_bytes) s.pool.push_back({s.stage_bytes, s.pool_bytes, false});
   L->prop.size = s.bytes;
   CUmemAllocationProp ap;
   memset(&ap, 0, sizeof(ap));
@@ -561,8 +571,8 @@ void nvls_setup(nbd_comm* c, uint64_t nonce_rank0) {
   DeviceGuard g(c->device);
   if (c->rank == 0) server(c);
   else client(c, nonce_rank0);
-  if (s.enabled) snprintf(s.why, sizeof(s.why), "enabled: %zu MiB staging per rank, granularity %zu KiB", s.bytes >> 20,
-                          s.granularity >> 10);
+  if (s.enabled) snprintf(s.why, sizeof(s.why), "enabled: %zu MiB staging + %zu MiB symmetric pool per rank, granularity %zu KiB",
+                          s.stage_bytes >> 20, s.pool_bytes >> 20, s.granularity >> 10);
   else nvls_teardown(c);
   const char* dbg = getenv("NBDIST_B200_DEBUG");
   if (dbg && dbg[0] != '0') fprintf(stderr, "[b200 nvls] rank %d: %s\n", c->rank, s.why);
@@ -600,4 +610,49 @@ void nvls_teardown(nbd_comm* c) {
     d.MemRelease(s.mem);
     s.have_mem = false;
   }
+}
+
+// Symmetric pool: first fit over address-ordered blocks, 2 MiB granules.  Every rank makes the
+// same calls in the same order (nbd_mem_alloc is collective), so every rank gets the same
+// offset; the descriptor check of the zero-copy kernels catches a rank that did not.
+char* nvls_pool_alloc(nbd_comm* c, size_t bytes, char** mc_alias) {
+  NvlsState& s = c->nvls;
+  if (!s.enabled || s.pool_bytes == 0 || bytes == 0) return nullptr;
+  const size_t need = round_up(bytes, 2ull << 20);
+  for (size_t k = 0; k < s.pool.size(); ++k) {
+    NvlsState::PoolBlock& b = s.pool[k];
+    if (b.used || b.len < need) continue;
+    const size_t off = b.off;
+    if (b.len > need) {
+      const NvlsState::PoolBlock rest = {b.off + need, b.len - need, false};
+      b.len = need;
+      b.used = true;
+      s.pool.insert(s.pool.begin() + (long)k + 1, rest);
+    } else {
+      b.used = true;
+    }
+    *mc_alias = s.mcva + off;
+    return s.local + off;
+  }
+  return nullptr;
+}
+
+bool nvls_pool_free(nbd_comm* c, char* ptr) {
+  NvlsState& s = c->nvls;
+  if (!s.local || ptr < s.local + s.stage_bytes || ptr >= s.local + s.bytes) return false;
+  const size_t off = (size_t)(ptr - s.local);
+  for (size_t k = 0; k < s.pool.size(); ++k) {
+    if (s.pool[k].off != off || !s.pool[k].used) continue;
+    s.pool[k].used = false;
+    if (k + 1 < s.pool.size() && !s.pool[k + 1].used) {
+      s.pool[k].len += s.pool[k + 1].len;
+      s.pool.erase(s.pool.begin() + (long)k + 1);
+    }
+    if (k > 0 && !s.pool[k - 1].used) {
+      s.pool[k - 1].len += s.pool[k].len;
+      s.pool.erase(s.pool.begin() + (long)k);
+    }
+    return true;
+  }
+  return false;
 }

@@ -338,7 +338,7 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
         __syncwarp();
       }
       const u64 tu = tile_units(g, i);
-      if (tu) warp_tile_copy(R, src, tile_first(g, i), tu, pb.local + slot_offset(g, i), true, lane);
+      if (tu && !(op.algo & 8)) warp_tile_copy(R, src, tile_first(g, i), tu, pb.local + slot_offset(g, i), true, lane);
       if (lane == 0) {
         bulk_wait_all0();     // the bulk stores into the slot are complete ...
         fence_proxy_async();  // ... and ordered before the generic-proxy release below
@@ -356,7 +356,7 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
       if (lane == 0) fence_proxy_async();  // acquired data is read by the async proxy next
       __syncwarp();
       const u64 tu = tile_units(g, i);
-      if (tu) warp_tile_copy(R, dst, tile_first(g, i), tu, pb.local + slot_offset(g, i), false, lane);
+      if (tu && !(op.algo & 16)) warp_tile_copy(R, dst, tile_first(g, i), tu, pb.local + slot_offset(g, i), false, lane);
       if (lane == 0) bulk_wait_all0();  // slot fully read, user memory written
       __syncwarp();
       if (lane == 0) {
@@ -382,7 +382,9 @@ k_allreduce_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
       u64 hi = lo + su;
       if (hi > tu) hi = tu;
       const u64 soff = slot_offset(g, i);
-      if (MC) {
+      if (op.algo & 32) {
+        // timing diagnostics only (pipe_mode bits 3-5 skip copy-in / copy-out / reduction)
+      } else if (MC) {
         if (op.algo & 4) mc_reduce_loop<T, 8>(pb.mc + soff, lo, hi, gt, nthr, op.avg, N);
         else mc_reduce_loop<T, 4>(pb.mc + soff, lo, hi, gt, nthr, op.avg, N);
       } else {
@@ -511,6 +513,45 @@ k_broadcast_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
     }
   }
   pipe_close(c, E, g.rounds, op);
+}
+
+// all_reduce on symmetric memory from the multicast pool (nbd_mem_alloc): no staging at all.
+// Barrier, rank r sums shard r inside the switch and writes it to every rank, barrier.
+// send_mc / recv_mc are multicast aliases; op.bytes is a multiple of 16 (the host checks).
+struct McPtrs {
+  const char* send_mc;
+  char* recv_mc;
+};
+template <typename T>
+__global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
+k_allreduce_mcz(const __grid_constant__ Pack<1> pk, const McPtrs m, const OpParams op) {
+  const RankCtx& c = pk.ctx[0];
+  const int N = c.world, r = c.rank;
+  KernelClock clk = kernel_begin(c);
+  flag_barrier(c, ++clk.epoch);
+  const u64 units = op.bytes / kUnit;
+  const u64 su = (units + N - 1) / N;
+  const u64 first = (u64)r * su;
+  const u64 mine = first >= units ? 0 : (units - first < su ? units - first : su);
+  u64 lo, hi;
+  block_span(su, mine, lo, hi);
+  const char* src = m.send_mc + first * kUnit;
+  char* dst = m.recv_mc + first * kUnit;
+  for (u64 b0 = lo + threadIdx.x; b0 < hi; b0 += 8ull * kThreads) {
+    uint4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const u64 u = b0 + (u64)j * kThreads;
+      if (u < hi) v[j] = McSum<T>::ld(src + u * kUnit);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const u64 u = b0 + (u64)j * kThreads;
+      if (u < hi) mc_st(dst + u * kUnit, op.avg ? unit_div<T>(v[j], N) : v[j]);
+    }
+  }
+  flag_barrier(c, ++clk.epoch);
+  kernel_end(c, 2, 0);
 }
 
 }  // namespace nbd

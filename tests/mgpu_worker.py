@@ -158,6 +158,35 @@ def body(rank: int, world: int, port: int) -> None:
         v.copy_(H.to_cuda(x[rank], "f32", dev))
         dist.all_reduce(v)
         H.assert_same(_np(v, "f32"), O.reduce_rank_order(x, "f32"), "f32", "in-switch sum on a storage_offset view")
+        # symmetric memory from the multicast pool (allocated while in-switch reduction is on):
+        # all_reduce needs no staging at all
+        pool = B.empty_symmetric((3 << 20) + 64, torch.float32)
+        for numel, off in (((3 << 20) + 64, 0), (1 << 20, 4096)):
+            xi = [np.random.default_rng(120 + r).integers(-1000, 1000, numel).astype(np.float32) for r in range(world)]
+            v = pool[off:off + numel]
+            v.copy_(H.to_cuda(xi[rank], "f32", dev))
+            dist.all_reduce(v)
+            assert be.last_algo() == "ar_nvls_zerocopy", be.last_algo()
+            H.assert_same(_np(v, "f32"), O.reduce_rank_order(xi, "f32"), "f32", f"zero-copy in-switch sum n={numel} off={off}")
+        x = O.make_inputs(world, 1 << 20, "bf16", seed=121)
+        pb = pool.view(torch.bfloat16)[: 1 << 20]
+        pb.copy_(H.to_cuda(x[rank], "bf16", dev))
+        dist.all_reduce(pb)
+        assert be.last_algo() == "ar_nvls_zerocopy"
+        err = np.abs(O.to_f64(_np(pb, "bf16"), "bf16") - O.to_f64(O.reduce_rank_order(x, "bf16"), "bf16"))
+        assert (err <= O.float_sum_tolerance(x, "bf16")).all(), "zero-copy in-switch bf16 sum"
+        # what the switch is not asked to do falls back to the staged kernels on the same memory
+        vi = pool.view(torch.int32)[: 70001]
+        xi = O.make_inputs(world, 70001, "i32", seed=122)
+        vi.copy_(H.to_cuda(xi[rank], "i32", dev))
+        dist.all_reduce(vi)
+        H.assert_same(_np(vi, "i32"), O.reduce_rank_order(xi, "i32"), "i32", "int32 on multicast-pool memory")
+        ragged = pool[7:7 + 100003]  # not a whole number of 16-byte units: staged in-switch pipeline
+        xr = [np.random.default_rng(130 + r).integers(-50, 50, 100003).astype(np.float32) for r in range(world)]
+        ragged.copy_(H.to_cuda(xr[rank], "f32", dev))
+        dist.all_reduce(ragged)
+        H.assert_same(_np(ragged, "f32"), O.reduce_rank_order(xr, "f32"), "f32", "ragged view of multicast-pool memory")
+        del pool, pb, vi, ragged, v
         be.set_tunable("nvls_reduce", 0)
         be.set_tunable("nvls_min_bytes", 0)
     # ---- the tile pipeline over peer-to-peer transport on real ranks: bit-exact ----------------

@@ -505,3 +505,38 @@ def test_ll_all_reduce_back_to_back(torch_cuda, groups, world):
         want = O.reduce_rank_order(x, dtype)
         for r in range(world):
             H.assert_same(H.to_numpy(out[r], dtype), want, dtype, f"op {i} rank {r}")
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_ll_broadcast_and_all_reduce_interleaved(torch_cuda, groups, world):
+    """The LL (flag-in-data) broadcast shares the two parity buffers with the LL all_reduce.  A
+    root needs nothing from its peers, so it could lap them: 60 back-to-back LL operations with
+    rotating roots and sizes, no host sync, exercise the ack back-pressure (kLLAckRow)."""
+    torch = torch_cuda
+    grp = groups(world)
+    rng = np.random.default_rng(11)
+    cases, outs = [], []
+    for it in range(60):
+        nbytes = int(rng.integers(1, 32 << 10))
+        if it % 3 == 2:
+            x = O.make_inputs(world, max(1, nbytes // 4), "f32", seed=300 + it)
+            t = [H.to_cuda(a, "f32") for a in x]
+            grp.all_reduce(t, t)
+            assert grp.last_algo() == "ar_ll"
+            cases.append(("ar", x, None))
+        else:
+            root = it % world
+            x = O.make_inputs(world, nbytes, "u8", seed=300 + it)
+            t = [H.to_cuda(a, "u8") for a in x]
+            grp.broadcast(t, root=root)
+            assert grp.last_algo() == "bcast_ll", grp.last_algo()
+            cases.append(("bc", x, root))
+        outs.append(t)
+    torch.cuda.synchronize()
+    grp.async_error()
+    for (kind, x, root), t in zip(cases, outs):
+        for r in range(world):
+            if kind == "ar":
+                H.assert_same(H.to_numpy(t[r], "f32"), O.reduce_rank_order(x, "f32"), "f32", f"LL all_reduce rank {r}")
+            else:
+                H.assert_same(H.to_numpy(t[r], "u8"), x[root], "u8", f"LL broadcast root {root} rank {r}")

@@ -23,8 +23,8 @@ def test_chunks_tile_the_message_and_fit_the_staging_half(world, stage, kind):
         half, chunk, n = p["half_bytes"], p["chunk_bytes"], p["nchunks"]
         assert half % UNIT == 0 and p["ll_off"] >= 2 * half
         assert 1 <= p["nblocks"] <= 512
-        if kind == "all_reduce" and p["algo"] == 3:  # LL: no staging halves involved
-            assert nbytes <= (32 << 10) and n == 1
+        if (kind == "all_reduce" and p["algo"] == 3) or (kind == "broadcast" and p["algo"] == 2):
+            assert nbytes <= (32 << 10) and n == 1  # LL: no staging halves involved
             continue
         assert chunk % UNIT == 0 and chunk > 0
         assert n * chunk >= nbytes > (n - 1) * chunk, (nbytes, chunk, n)
@@ -51,6 +51,8 @@ def test_algorithm_thresholds():
     assert capi.plan_query(8, "all_reduce", 2 << 20)["algo"] == 1
     assert capi.plan_query(8, "all_reduce", (2 << 20) + 16)["algo"] == 2  # two-shot
     assert capi.plan_query(2, "all_reduce", 1 << 30)["algo"] == 1         # two ranks: always one-shot
+    assert capi.plan_query(8, "broadcast", 4096)["algo"] == 2                # LL
+    assert capi.plan_query(8, "broadcast", (32 << 10) + 16)["algo"] == 0     # direct
     assert capi.plan_query(8, "broadcast", 256 << 10)["algo"] == 0
     assert capi.plan_query(8, "broadcast", (256 << 10) + 16)["algo"] == 1
     assert capi.plan_query(2, "broadcast", 1 << 30)["algo"] == 0

@@ -94,9 +94,9 @@ def main():
             per4 = -(-nbytes // (148 * 4) // 128) * 128
             per2 = -(-nbytes // (148 * 2) // 128) * 128
             per8 = -(-nbytes // (148 * 8) // 128) * 128
-            for tile in (per8, 256 << 10 if nbytes > (64 << 20) else per4, per4, per2):
-                for depth in (3, 4):
-                    for mode in (0, 2, 4, 6):
+            for tile in ((256 << 10 if nbytes > (64 << 20) else per4),):
+                for depth in (4,):
+                    for mode in (0, 2):
                         kv = {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "pipe_depth": depth, "pipe_mode": mode}
                         with knobs(**kv):
                             x.copy_(src)
@@ -107,6 +107,14 @@ def main():
                             us = timed(lambda: dist.all_reduce(x), 10)
                         emit({"op": "all_reduce", "variant": f"nvls/tile={tile}/depth={depth}/mode={mode}", "bytes": nbytes,
                               "us": round(us, 2), "busbw": round(nbytes * f_ar / us / 1e3, 1), "algo": algo, "ok": ok})
+            # where the time goes: the same launch with copy-in (8), copy-out (16) or the in-switch
+            # reduction (32) skipped (results are void; timing only)
+            for mode in (8, 16, 24, 32, 40, 48, 56):
+                kv = {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_mode": mode}
+                with knobs(**kv):
+                    us = timed(lambda: dist.all_reduce(x), 10)
+                emit({"op": "all_reduce", "variant": f"nvls-diag/skip={mode}", "bytes": nbytes, "us": round(us, 2),
+                      "busbw": round(nbytes * f_ar / us / 1e3, 1)})
             with knobs(auto_min_bytes=1 << 20, pipe=2, nvls_off=1):
                 for _ in range(3):
                     dist.all_reduce(x)

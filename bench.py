@@ -157,12 +157,19 @@ def nvlink_bytes(device_index: int):
         h = nv.nvmlDeviceGetHandleByIndex(device_index)
         vals = nv.nvmlDeviceGetFieldValues(h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
                                                (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)])
-        out = []
-        for v in vals:
-            if v.nvmlReturn != 0:
-                return None
-            out.append(int(v.value.ullVal) * 1024)
-        return tuple(out)
+        if all(v.nvmlReturn == 0 for v in vals):
+            return tuple(int(v.value.ullVal) * 1024 for v in vals)
+        # no aggregate scope on this driver: sum the 18 links
+        tx = rx = 0
+        got = False
+        for link in range(18):
+            vals = nv.nvmlDeviceGetFieldValues(h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, link),
+                                                   (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, link)])
+            if all(v.nvmlReturn == 0 for v in vals):
+                tx += int(vals[0].value.ullVal) * 1024
+                rx += int(vals[1].value.ullVal) * 1024
+                got = True
+        return (tx, rx) if got else None
     except Exception:
         return None
 
@@ -485,7 +492,7 @@ def parity_check(torch, dist, dev, rank, world, cpu_group, be, B):
     nv_on, nv_why = be.nvls_status()
     notes.append(f"multicast: {'on' if nv_on else 'off'} ({nv_why})")
     if nv_on:
-        be.set_tunable("nvls_reduce", 1)
+        be.set_tunable("nvls_reduce", 2)  # 2: also between two ranks
         n = (4 << 20) + 3
         x = _seeded(torch, dev, rank, n, torch.float32, 4900)
         y = x.clone()
@@ -643,6 +650,8 @@ def run_ours_multi(args):
             log("in-switch reduction sweep")
             be.set_tunable("nvls_reduce", 1)
             extras["nvls_sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be, only_all_reduce=True)
+            log("in-switch reduction on multicast-pool memory (zero copy)")
+            extras["nvls_registered"] = nvls_registered_sweep(torch, dist, dev, world, cpu_group, be)
             be.set_tunable("nvls_reduce", 0)
         log("device-side small-message latency")
         extras["latency"] = kernel_latency(torch, dist, dev, world, cpu_group, be)
@@ -718,6 +727,31 @@ def registered_sweep(torch, dist, dev, world, cpu_group, be):
     return out
 
 
+def nvls_registered_sweep(torch, dist, dev, world, cpu_group, be):
+    """all_reduce on symmetric memory allocated while in-switch reduction is on: the buffer is
+    bound into the multicast object, so the kernel is barrier, multimem.ld_reduce + multimem.st
+    of the rank's shard, barrier - no staging."""
+    from nbdistributed_b200 import backend as B
+
+    out = []
+    try:
+        big = B.empty_symmetric((1 << 30) // 4, torch.float32)
+    except Exception as e:  # noqa: BLE001
+        return [{"unavailable": str(e)[:160]}]
+    for nbytes in (1 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30):
+        buf = big[: nbytes // 4]
+        buf.fill_(1.0)
+        dist.all_reduce(buf)
+        ok = bool((buf == float(world)).all())
+        buf.zero_()
+        iters = 50 if nbytes <= (1 << 20) else (20 if nbytes <= (64 << 20) else 5)
+        ms = _time_collective(torch, dist, lambda: dist.all_reduce(buf), iters, 3, cpu_group)
+        out.append({"op": "all_reduce", "dtype": "float32", "bytes": nbytes, "us": round(ms * 1e3, 2), "ok": ok,
+                    "busbw_per_rank": round(nbytes * bus_factor(world) / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
+    del big
+    return out
+
+
 def multi_sweep(torch, dist, dev, world, cpu_group, be, only_all_reduce=False):
     out = []
     if not only_all_reduce:
@@ -774,6 +808,21 @@ def kernel_latency(torch, dist, dev, world, cpu_group, be):
         t = torch.tensor([e0.elapsed_time(e1) * 1e3 / iters], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
         out.append({"op": "all_reduce", "bytes": nbytes, "us": round(float(t.item()), 2), "algo": be.last_algo()})
+    for nbytes in (8, 4 << 10, 32 << 10, 256 << 10):
+        buf = torch.zeros(max(1, nbytes // 4), device=dev, dtype=torch.float32)
+        iters = 200
+        be.repeat_broadcast(buf, 0, 20)
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        be.repeat_broadcast(buf, 0, iters)
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
+        t = torch.tensor([e0.elapsed_time(e1) * 1e3 / iters], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
+        out.append({"op": "broadcast", "bytes": nbytes, "us": round(float(t.item()), 2), "algo": be.last_algo()})
     return out
 
 

@@ -132,7 +132,7 @@ class WorkB200 : public c10d::Work {
   }
 
   bool isCompleted() override { return done_.query(); }
-  bool isSuccess() const override { return nbd_comm_async_error(comm_) == NBD_OK; }
+  bool isSuccess() const override { return !comm_ || nbd_comm_async_error(comm_) == NBD_OK; }
 
   void synchronize() override {
     auto cur = c10::cuda::getCurrentCUDAStream(dev_);
@@ -155,13 +155,13 @@ class WorkB200 : public c10d::Work {
       const auto deadline = std::chrono::steady_clock::now() + timeout;
       while (!done_.query()) {
         if (std::chrono::steady_clock::now() >= deadline) {
-          nbd_comm_abort(comm_);
+          if (comm_) nbd_comm_abort(comm_);
           C10_THROW_ERROR(DistBackendError, c10::str("[", kBackendName, "] wait(timeout=", timeout.count(),
                                                      " ms) expired; the communicator was aborted"));
         }
         std::this_thread::sleep_for(std::chrono::microseconds(50));
       }
-      const int rc = nbd_comm_async_error(comm_);
+      const int rc = comm_ ? nbd_comm_async_error(comm_) : (int)NBD_OK;
       if (rc != NBD_OK) throw_nbd(rc, "wait");
     }
     synchronize();
@@ -288,7 +288,7 @@ class BackendB200 : public c10d::Backend {
       if (coalescing_ && (size_t)t.nbytes() <= kCoalesceMaxBytes) {  // small: one table launch at endCoalescing
         co_bcast_.push_back({t, root});
         co_tensors_.push_back(t);
-        return c10::intrusive_ptr<c10d::Work>();
+        return collected_work(t);
       }
     }
     return run(c10d::OpType::BROADCAST, "b200:broadcast", t.get_device(), {t}, {t}, opts.asyncOp, false,
@@ -715,6 +715,21 @@ class BackendB200 : public c10d::Backend {
     has_last_ = true;
   }
 
+  // Same for broadcast (root's tensor to everybody), `iters` times back to back.
+  void repeat_broadcast(at::Tensor t, int64_t root, int64_t iters) {
+    check_tensor(t);
+    std::lock_guard<std::mutex> lk(mu_);
+    ensure_comm(t.get_device());
+    c10::cuda::CUDAGuard g(t.get_device());
+    auto stream = c10::cuda::getCurrentCUDAStream(t.get_device());
+    if (has_last_ && *last_stream_ != stream) last_done_.block(stream);
+    for (int64_t i = 0; i < iters; ++i)
+      NBD_CHECK(nbd_broadcast(comm_, t.data_ptr(), (size_t)t.nbytes(), NBD_BYTES, (int)root, stream.stream()), "repeat_broadcast");
+    last_done_.record(stream);
+    last_stream_ = stream;
+    has_last_ = true;
+  }
+
   // all_reduce of CPU tensors through the GPUs: nbd_all_reduce_host pipelines H2D, the
   // collective and D2H in chunks.  Returns when `recv` holds the result (CPU-tensor semantics).
   void all_reduce_host(at::Tensor send, at::Tensor recv, int64_t op) {
@@ -763,6 +778,16 @@ class BackendB200 : public c10d::Backend {
     int root;
   };
 
+  // What an operation collected by a coalescing block returns: a Work that is already complete
+  // (the real one comes from endCoalescing).  Not null: the call travels through the dispatcher.
+  c10::intrusive_ptr<c10d::Work> collected_work(const at::Tensor& t) {
+    auto work = c10::make_intrusive<WorkB200>(getRank(), c10d::OpType::COALESCED, "b200:collected", t.get_device(), nullptr,
+                                              std::vector<at::Tensor>{t}, false);
+    c10::cuda::CUDAGuard g(t.get_device());
+    work->mark_enqueued(c10::cuda::getCurrentCUDAStream(t.get_device()));
+    return work;
+  }
+
   c10::intrusive_ptr<c10d::Work> p2p_one(std::vector<at::Tensor>& tensors, int peer, int kind, c10d::OpType type, const char* title) {
     TORCH_CHECK(tensors.size() == 1, "[b200] send/recv expect exactly one tensor");
     auto& t = tensors[0];
@@ -774,7 +799,7 @@ class BackendB200 : public c10d::Backend {
       if (coalescing_) {  // collected; endCoalescing launches the whole batch and returns its Work
         co_ops_.push_back({kind, peer, t.data_ptr(), (size_t)t.nbytes()});
         co_tensors_.push_back(t);
-        return c10::intrusive_ptr<c10d::Work>();
+        return collected_work(t);
       }
     }
     return run(type, title, t.get_device(), {t}, {t}, /*async_op=*/true, false, [&](cudaStream_t s) {
@@ -914,6 +939,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("all_reduce_host", &BackendB200::all_reduce_host, py::arg("send"), py::arg("recv"), py::arg("op") = 0,
            py::call_guard<py::gil_scoped_release>())
       .def("repeat_all_reduce", &BackendB200::repeat_all_reduce, py::call_guard<py::gil_scoped_release>())
+      .def("repeat_broadcast", &BackendB200::repeat_broadcast, py::call_guard<py::gil_scoped_release>())
       .def("device_index", &BackendB200::device_index)
       .def("set_inline_sync_ops", &BackendB200::set_inline_sync_ops);
   m.def("create_backend", &create_backend, py::arg("store"), py::arg("rank"), py::arg("size"), py::arg("timeout"),

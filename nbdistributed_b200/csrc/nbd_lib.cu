@@ -694,7 +694,9 @@ static const u64 kDefNvlsReduceMin = 1ull << 20;
 static const u64 kDefNvlsBcastMin = 512ull << 10;
 
 static bool nvls_reduce_wanted(const nbd_comm* c, u64 bytes, int dtype, int op) {
-  return c->nvls.enabled && !c->t_nvls_off && c->t_nvls_reduce && (op == NBD_SUM || op == NBD_AVG) &&
+  // two ranks: the switch path moves 1.5 S per direction against S peer to peer (2xB200, 256 MiB:
+  // 326 vs 602 GB/s); from four ranks on it moves less (S(1+1/N) against 2(N-1)/N S)
+  return c->nvls.enabled && (c->world > 2 || c->t_nvls_reduce == 2) && !c->t_nvls_off && c->t_nvls_reduce && (op == NBD_SUM || op == NBD_AVG) &&
          (dtype == NBD_F32 || dtype == NBD_BF16 || dtype == NBD_F16) &&
          bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsReduceMin);
 }

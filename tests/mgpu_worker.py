@@ -113,7 +113,7 @@ def body(rank: int, world: int, port: int) -> None:
         dist.broadcast(v, src=1 % world)
         H.assert_same(_np(v, "u8"), x[1 % world], "u8", "multicast broadcast into a misaligned view")
         be.set_tunable("nvls_bcast", 0)
-        be.set_tunable("nvls_reduce", 1)
+        be.set_tunable("nvls_reduce", 2)  # 2: also between two ranks, where 1 leaves it to the peer-to-peer kernels
         for mode in (0, 2, 6):  # one / two reducing groups, 4 / 8 loads in flight
             be.set_tunable("pipe_mode", mode)
             xi = [np.random.default_rng(60 + r).integers(-1000, 1000, (2 << 20) + 11).astype(np.float32) for r in range(world)]
@@ -332,6 +332,89 @@ def body(rank: int, world: int, port: int) -> None:
     B.all_reduce_host(hf)
     H.assert_same(hf.numpy(), O.reduce_rank_order(O.make_inputs(world, 300001, "f32", seed=61), "f32"), "f32", "all_reduce_host f32")
     be.set_tunable("host_chunk_bytes", 0)
+
+    # ---- point to point and what is built on it, against gloo on the same data ----------------
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+    for numel in (1, 4099, (3 << 20) + 5):
+        a = H.to_cuda(O.make_inputs(world, numel, "f32", seed=200)[rank], "f32", dev)
+        b = torch.empty_like(a)
+        if rank % 2 == 0:  # blocking calls: pair them up so that they cannot deadlock
+            dist.send(a, nxt)
+            dist.recv(b, prv)
+        else:
+            dist.recv(b, prv)
+            dist.send(a, nxt)
+        H.assert_same(_np(b, "f32"), O.make_inputs(world, numel, "f32", seed=200)[prv], "f32", f"send/recv ring n={numel}")
+        # the same exchange as one batch: order inside the batch does not matter
+        b2 = torch.zeros_like(a)
+        reqs = dist.batch_isend_irecv([dist.P2POp(dist.isend, a, nxt), dist.P2POp(dist.irecv, b2, prv)])
+        for q in reqs:
+            q.wait()
+        assert torch.equal(b2, b), "batch_isend_irecv differs from send/recv"
+    x = O.make_inputs(world, world * 70001, "i32", seed=201)
+    t_in = H.to_cuda(x[rank], "i32", dev)
+    t_out = torch.empty_like(t_in)
+    dist.all_to_all_single(t_out, t_in)
+    want = np.concatenate([x[s][rank * 70001:(rank + 1) * 70001] for s in range(world)])
+    H.assert_same(_np(t_out, "i32"), want, "i32", "all_to_all_single")
+    splits_in = [(rank + p) % 3 + 1 for p in range(world)]              # what I send to p
+    splits_out = [(s + rank) % 3 + 1 for s in range(world)]             # what s sends to me
+    ti = torch.arange(sum(splits_in) * 5, device=dev, dtype=torch.float32).reshape(-1, 5) + 1000 * rank
+    to = torch.empty(sum(splits_out), 5, device=dev)
+    dist.all_to_all_single(to, ti, output_split_sizes=splits_out, input_split_sizes=splits_in)
+    ci, co = ti.cpu(), torch.empty(sum(splits_out), 5)
+    dist.all_to_all_single(co, ci, output_split_sizes=splits_out, input_split_sizes=splits_in)  # gloo
+    assert torch.equal(to.cpu(), co), "all_to_all_single with split sizes differs from gloo"
+    outs = [torch.empty(1000 + 7 * s, device=dev) for s in range(world)]
+    ins = [torch.full((1000 + 7 * rank,), float(100 * rank + p), device=dev) for p in range(world)]
+    dist.all_to_all(outs, ins)
+    for s_ in range(world):
+        assert bool((outs[s_] == float(100 * s_ + rank)).all()), "all_to_all list form"
+    for root in sorted({0, world - 1}):
+        g_in = H.to_cuda(O.make_inputs(world, 33333, "bf16", seed=202)[rank], "bf16", dev)
+        g_out = [torch.empty_like(g_in) for _ in range(world)] if rank == root else None
+        dist.gather(g_in, g_out, dst=root)
+        if rank == root:
+            for s_ in range(world):
+                H.assert_same(_np(g_out[s_], "bf16"), O.make_inputs(world, 33333, "bf16", seed=202)[s_], "bf16", f"gather slot {s_}")
+        sc_out = torch.empty(4097, device=dev)
+        sc_in = [torch.full((4097,), float(p + 1), device=dev) for p in range(world)] if rank == root else None
+        dist.scatter(sc_out, sc_in, src=root)
+        assert bool((sc_out == float(rank + 1)).all()), "scatter"
+        xr = O.make_inputs(world, 50001, "f32", seed=203)
+        tr = H.to_cuda(xr[rank], "f32", dev)
+        dist.reduce(tr, dst=root)
+        if rank == root:
+            H.assert_same(_np(tr, "f32"), O.reduce_rank_order(xr, "f32"), "f32", "reduce at the root")
+        else:
+            H.assert_same(_np(tr, "f32"), xr[rank], "f32", "reduce must leave non-root tensors alone")
+    # ---- coalescing: the reference's per-parameter broadcast loop as ONE table launch ----------
+    torch.manual_seed(rank)
+    params = [torch.randn(n, device=dev) for n in (768, 768, 2304, 10, 3072, 1, 768 * 4)] + [torch.randn(1 << 20, device=dev)]
+    ref = [p.cpu().clone() for p in params]
+    n0 = B.launch_count()
+    with dist._coalescing_manager(device=dev):
+        for p in params:
+            dist.broadcast(p, src=0)
+    torch.cuda.synchronize()
+    launches = B.launch_count() - n0
+    for q in ref:
+        dist.broadcast(q, src=0)  # gloo
+    for p, q in zip(params, ref):
+        assert torch.equal(p.cpu(), q), "coalesced broadcast differs from gloo"
+    assert launches <= 2, f"7 small + 1 large broadcast took {launches} launches"
+    # ---- sub-groups: dist.new_group over a subset gets its own communicator ----------------------
+    if world >= 4:
+        evens = dist.new_group(ranks=list(range(0, world, 2)), backend="cpu:gloo,cuda:b200")
+        if rank % 2 == 0:
+            xs = O.make_inputs(world, 100003, "f32", seed=204)
+            ts = H.to_cuda(xs[rank], "f32", dev)
+            dist.all_reduce(ts, group=evens)
+            H.assert_same(_np(ts, "f32"), O.reduce_rank_order([xs[r] for r in range(0, world, 2)], "f32"), "f32", "sub-group all_reduce")
+            tb = H.to_cuda(xs[rank], "f32", dev)
+            dist.broadcast(tb, src=2, group=evens)
+            H.assert_same(_np(tb, "f32"), xs[2], "f32", "sub-group broadcast")
+        dist.barrier()
 
     # ---- async ops, futures, barrier, non-contiguous rejection -----------------------------
     x = O.make_inputs(world, 1 << 20, "f32", seed=3)

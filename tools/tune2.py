@@ -97,7 +97,7 @@ def main():
             for tile in ((256 << 10 if nbytes > (64 << 20) else per4),):
                 for depth in (4,):
                     for mode in (0, 2):
-                        kv = {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "pipe_depth": depth, "pipe_mode": mode}
+                        kv = {"nvls_reduce": 2, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "pipe_depth": depth, "pipe_mode": mode}
                         with knobs(**kv):
                             x.copy_(src)
                             dist.all_reduce(x)
@@ -110,7 +110,7 @@ def main():
             # where the time goes: the same launch with copy-in (8), copy-out (16) or the in-switch
             # reduction (32) skipped (results are void; timing only)
             for mode in (8, 16, 24, 32, 40, 48, 56):
-                kv = {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_mode": mode}
+                kv = {"nvls_reduce": 2, "nvls_min_bytes": 1, "pipe_mode": mode}
                 with knobs(**kv):
                     us = timed(lambda: dist.all_reduce(x), 10)
                 emit({"op": "all_reduce", "variant": f"nvls-diag/skip={mode}", "bytes": nbytes, "us": round(us, 2),
@@ -139,7 +139,7 @@ def main():
         for tile in (0, 128 << 10):
             for blocks in (0, 96):
                 ar_variants.append((f"nvls/tile={tile >> 10}K/blocks={blocks}",
-                                    {"nvls_reduce": 1, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "blocks": blocks}))
+                                    {"nvls_reduce": 2, "nvls_min_bytes": 1, "pipe_tile_bytes": tile, "blocks": blocks}))
     for nbytes in sizes:
         n = nbytes // 4
         x = big[:n]
@@ -174,7 +174,7 @@ def main():
     x = big[: nbytes // 4]
     dvariants = [("auto", {"auto_min_bytes": 1 << 20, "pipe": 2, "nvls_off": 1})]
     if have_nvls:
-        dvariants.append(("nvls", {"nvls_reduce": 1, "nvls_min_bytes": 1}))
+        dvariants.append(("nvls", {"nvls_reduce": 2, "nvls_min_bytes": 1}))
     for data in ("zeros", "ones", "randn"):
         def fill():
             if data == "zeros":

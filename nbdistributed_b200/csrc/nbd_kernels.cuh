@@ -52,6 +52,26 @@ __device__ __forceinline__ const ZcPtrs& zc_ptrs(const RankCtx& c, const PackZc<
   return pk.z;
 }
 
+// Ranks must run the same KIND of kernel for a collective.  A rank whose buffers are registered
+// (symmetric memory) runs the zero-copy kernel and publishes a descriptor tagged with its epoch
+// before the opening barrier (zc_publish_desc); a rank that passed ordinary buffers runs the
+// staged kernel.  The zero-copy side notices (the staged peer published nothing: stale tag);
+// this is the staged side's half: after its first barrier, a descriptor carrying OUR epoch's tag
+// means that peer is in a zero-copy kernel -> NBD_ERR_MISMATCH instead of silent garbage.
+template <int NCTX>
+__device__ __forceinline__ void staged_check_peers(const RankCtx& c, u64 tag) {
+  if (NCTX != 1 || blockIdx.x != 0) return;
+  const int t = threadIdx.x;
+  if (t < c.world && t != c.rank) {
+    const volatile u64* d = c.flags[c.rank] + (u64)(kDescRow + t) * kMaxRanks;
+    if (d[6] == tag) {
+      volatile HostMailbox* mb = c.mbox;
+      mb->error = 8;  // -NBD_ERR_MISMATCH
+      reinterpret_cast<volatile LocalState*>(c.state)->failed = 1;
+    }
+  }
+}
+
 // N-way reduce of units [lo,hi) with U units per thread in flight: src(k, i) loads unit i of
 // rank k's contribution, dst(i, v) stores the result.  Ascending k; U*N <= 8 loads outstanding
 // per thread, so few ranks get a deeper unroll (remote loads need the bytes in flight).
@@ -163,6 +183,7 @@ k_allreduce_oneshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   if (op.nchunks) push(0);
   for (u32 cidx = 0; cidx < op.nchunks; ++cidx) {
     flag_barrier(c, ++clk.epoch);
+    if (cidx == 0) staged_check_peers<NCTX>(c, clk.epoch);
     if (cidx + 1 < op.nchunks) push(cidx + 1);
     const u64 off = (u64)cidx * op.chunk_bytes;
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
@@ -396,6 +417,7 @@ k_allreduce_twoshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   if (op.nchunks) push(0);
   for (u32 cidx = 0; cidx < op.nchunks; ++cidx) {
     flag_barrier(c, ++clk.epoch);
+    if (cidx == 0) staged_check_peers<NCTX>(c, clk.epoch);
     if (cidx + 1 < op.nchunks) push(cidx + 1);
 
     const u64 off = (u64)cidx * op.chunk_bytes;
@@ -468,6 +490,7 @@ k_reduce_scatter(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   if (op.nchunks) push(0);
   for (u32 cidx = 0; cidx < op.nchunks; ++cidx) {
     flag_barrier(c, ++clk.epoch);
+    if (cidx == 0) staged_check_peers<NCTX>(c, clk.epoch);
     if (cidx + 1 < op.nchunks) push(cidx + 1);
     const u64 off = (u64)cidx * op.chunk_bytes;
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
@@ -506,6 +529,7 @@ k_all_gather(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   if (op.nchunks) copyin(0);
   for (u32 cidx = 0; cidx < op.nchunks; ++cidx) {
     flag_barrier(c, ++clk.epoch);
+    if (cidx == 0) staged_check_peers<NCTX>(c, clk.epoch);
     if (cidx + 1 < op.nchunks) copyin(cidx + 1);
     const u64 off = (u64)cidx * op.chunk_bytes;
     const u64 cb = clip_bytes(op.bytes, off, op.chunk_bytes);
@@ -673,6 +697,7 @@ __device__ __forceinline__ void zc_check_desc(const RankCtx& c, const ZcPtrs& z,
     if (!same) {
       volatile HostMailbox* mb = c.mbox;
       mb->error = 8;  // -NBD_ERR_MISMATCH
+      reinterpret_cast<volatile LocalState*>(c.state)->failed = 1;  // later flag waits of this launch drain
     }
   }
 }

@@ -471,6 +471,23 @@ def body(rank: int, world: int, port: int) -> None:
     assert all(int(a) == int(allchk[0]) for a in allchk), "ranks disagree bit-wise on a 256 MiB all_reduce"
     del big, ref, bigf
     torch.cuda.synchronize()
+
+    # ---- LAST (it kills the communicator): one rank passes symmetric memory, the others an
+    # ordinary tensor.  The ranks then run different kernels; both kinds must notice and report
+    # NBD_ERR_MISMATCH instead of returning garbage or hanging.
+    be.set_tunable("zc_min_bytes", 256 << 10)
+    be.set_tunable("auto_register_off", 1)
+    symm = B.empty_symmetric(1 << 20, torch.float32)
+    plain = torch.ones(1 << 20, device=dev)
+    symm.fill_(1.0)
+    dist.all_reduce(symm if rank == 0 else plain)
+    torch.cuda.synchronize()
+    try:
+        dist.all_reduce(plain)
+        torch.cuda.synchronize()
+        raise AssertionError("mixed registered/unregistered buffers went unnoticed")
+    except RuntimeError as e:
+        assert "different registered buffers" in str(e) or "MISMATCH" in str(e).upper() or "aborted" in str(e), e
     W.shutdown_worker()
 
 

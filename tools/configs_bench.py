@@ -92,9 +92,29 @@ def main():
     ms3 = timed(bcast_all, 5, 1)
     small = [t for t in tensors if t.numel() * 4 <= 12 * 1024]
     ms_small = timed(lambda: [dist.broadcast(t, src=0) for t in small], 5, 1)
-    emit({"config": "cfg3 GPT-2 small state_dict broadcast", "ranks": world, "tensors": len(tensors), "bytes": total,
-          "identical_on_all_ranks": ok3, "ms_total": round(ms3, 3), "effective_GBps": round(total / ms3 / 1e6, 1),
-          "small_tensors": len(small), "us_per_small_broadcast": round(ms_small * 1e3 / len(small), 2)})
+    # the same loop inside a c10d coalescing block: the 98 small tensors become one table launch
+    def bcast_coalesced():
+        with dist._coalescing_manager(device=dev):
+            for t in tensors:
+                dist.broadcast(t, src=0)
+
+    for t in tensors[1:]:
+        if rank != 0:
+            t.zero_()
+    bcast_coalesced()
+    torch.cuda.synchronize()
+    chk2 = torch.stack([t.view(torch.int32).sum(dtype=torch.int64) for t in tensors]).cpu()
+    ok3c = bool(torch.equal(chk2, allc[0]))
+    ms3c = timed(bcast_coalesced, 5, 1)
+    line3 = {"config": "cfg3 GPT-2 small state_dict broadcast", "ranks": world, "tensors": len(tensors), "bytes": total,
+             "identical_on_all_ranks": ok3, "ms_total": round(ms3, 3), "effective_GBps": round(total / ms3 / 1e6, 1),
+             "small_tensors": len(small), "us_per_small_broadcast": round(ms_small * 1e3 / len(small), 2),
+             "coalesced_ms_total": round(ms3c, 3), "coalesced_identical": ok3c,
+             "coalesced_effective_GBps": round(total / ms3c / 1e6, 1)}
+    if nccl is not None:
+        ms3n = timed(lambda: [dist.broadcast(t, src=0, group=nccl) for t in tensors], 5, 1)
+        line3["nccl_ms_total"] = round(ms3n, 3)
+    emit(line3)
     del tensors
 
     # ---------------- cfg4: DDP-style bf16 gradient buckets, 1.236 G params ----------------

@@ -493,6 +493,7 @@ def parity_check(torch, dist, dev, rank, world, cpu_group, be, B):
     notes.append(f"multicast: {'on' if nv_on else 'off'} ({nv_why})")
     if nv_on:
         be.set_tunable("nvls_reduce", 2)  # 2: also between two ranks
+        be.set_tunable("nvls_min_bytes", 1)  # the staged in-switch pipeline is only the default from 128 MiB on
         n = (4 << 20) + 3
         x = _seeded(torch, dev, rank, n, torch.float32, 4900)
         y = x.clone()
@@ -513,6 +514,7 @@ def parity_check(torch, dist, dev, rank, world, cpu_group, be, B):
         dist.all_reduce(wi)
         check("in-switch all_reduce of integer-valued fp32 (exact)", torch.equal(yi, wi.to(torch.float32)))
         be.set_tunable("nvls_reduce", 0)
+        be.set_tunable("nvls_min_bytes", 0)
     torch.cuda.synchronize()
     res = {"world": world, "cases": cases, "failed": len(failed), "algos": sorted(algos), "notes": notes}
     if failed:

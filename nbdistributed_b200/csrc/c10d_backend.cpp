@@ -322,16 +322,23 @@ class BackendB200 : public c10d::Backend {
                   "[b200] all_gather: every output tensor must match the input's dtype and size");
     }
     std::vector<at::Tensor> all_out(list.begin(), list.end());
+    all_out.push_back(in);
+    const int N = getSize(), me = getRank();
     return run(c10d::OpType::ALLGATHER, "b200:all_gather", in.get_device(), {in}, all_out, opts.asyncOp, false,
                [&](cudaStream_t s) {
-                 // gather into one flat buffer, then scatter to the caller's list on the same stream
-                 at::Tensor flat = at::empty({(int64_t)getSize() * in.numel()}, in.options());
-                 note_stream(flat);
-                 int rc = nbd_all_gather(comm_, in.data_ptr(), flat.data_ptr(), (size_t)in.nbytes(), NBD_BYTES, s);
-                 if (rc != NBD_OK) return rc;
-                 for (int r = 0; r < getSize(); ++r)
-                   list[r].copy_(flat.narrow(0, (int64_t)r * in.numel(), in.numel()).view_as(list[r]), true);
-                 return (int)NBD_OK;
+                 // straight into the caller's list: one point-to-point batch (a send to and a
+                 // receive from every peer, all concurrent) plus the local copy - no flat
+                 // temporary, no scatter copies
+                 std::vector<nbd_p2p_op> ops;
+                 for (int k = 1; k < N; ++k) ops.push_back({NBD_P2P_SEND, (me + k) % N, in.data_ptr(), (size_t)in.nbytes()});
+                 for (int k = 1; k < N; ++k) {
+                   const int p = (me - k + N) % N;
+                   ops.push_back({NBD_P2P_RECV, p, list[p].data_ptr(), (size_t)list[p].nbytes()});
+                 }
+                 if (in.nbytes() > 0 && list[me].data_ptr() != in.data_ptr())
+                   if (cudaMemcpyAsync(list[me].data_ptr(), in.data_ptr(), (size_t)in.nbytes(), cudaMemcpyDeviceToDevice, s) != cudaSuccess)
+                     return (int)NBD_ERR_CUDA;
+                 return nbd_p2p_batch(comm_, ops.data(), (int)ops.size(), s);
                });
   }
 

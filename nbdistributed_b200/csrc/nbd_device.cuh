@@ -37,6 +37,7 @@ struct LocalState {
   u32 done;       // CTAs of the running launch that have finished
   u32 failed;     // set (never cleared) when a flag wait of this rank gave up: later waits drain
   u64 ll_seq;     // LL (flag-in-data) operations completed; parity picks the LL buffer
+  u64 ll_hist;    // bit 0: the last LL operation was a broadcast; bit 1: the one before it was
 };
 
 // Pinned host memory, visible to the device: async error reporting + abort.
@@ -67,11 +68,12 @@ struct RankCtx {
 constexpr u64 kLLMaxBytes = 32ull << 10;
 constexpr u64 kLLSlotBytes = 2 * kLLMaxBytes;
 constexpr u64 kLLAreaBytes = 2 * (u64)kMaxRanks * kLLSlotBytes;  // 1 MiB
-// Row of the flag array where rank `src` publishes "LL operations I have finished reading" (word
-// = src).  A rank that WRITES packets for LL operation s first checks that every receiver has
-// finished operation s-2, the previous user of the same parity buffer: with all_reduce alone
-// that is implied (one cannot get two operations ahead of a peer whose packets one needs), but
-// the root of an LL broadcast needs nothing from its peers and could otherwise lap them.
+// Row of the flag array where rank `src` publishes "LL broadcasts I have finished reading" (word
+// = src, value = sequence number + 1).  A rank that WRITES packets for LL operation s must know
+// that every receiver has finished operation s-2, the previous user of the same parity buffer.
+// After an all_reduce that is implied (one has received every peer's packets of s-1, which they
+// sent after finishing s-2); a broadcast's root hears nothing from its peers, so broadcasts are
+// acknowledged, and only an operation that directly follows a broadcast has to look (ll_hist).
 constexpr int kLLAckRow = 480;
 
 struct RankBufs {

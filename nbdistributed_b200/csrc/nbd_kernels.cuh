@@ -216,21 +216,24 @@ __device__ __forceinline__ uint4 ld_ll(const char* p) {
 }
 
 // Before writing packets of LL operation `seq`: every receiver has finished operation seq - 2.
-__device__ __forceinline__ void ll_wait_acks(const RankCtx& c, u64 seq) {
+// Only needed when operation seq - 1 was a broadcast (see kLLAckRow): if seq - 2 was one too its
+// ack says so directly, otherwise the ack of seq - 1 implies it.
+__device__ __forceinline__ void ll_wait_acks(const RankCtx& c, u64 seq, u64 hist) {
+  if (!(hist & 1)) return;  // uniform across the CTA
   const int t = threadIdx.x;
-  if (seq >= 2 && t < c.world && t != c.rank) {
+  if (t < c.world && t != c.rank) {
     // no acquire fence: nothing is READ on the strength of the ack, we only write afterwards,
-    // and a store is never performed ahead of the load it depends on (the fence cost ~2.5 us of
-    // the 6 us an LL all_reduce takes)
+    // and a store is never performed ahead of the load it depends on
+    const u64 need = (hist & 2) ? seq - 1 : seq;
     const u64* f = c.flags[c.rank] + (u64)kLLAckRow * kMaxRanks + t;
-    if (ld_relaxed_sys(f) < seq - 1) wait_flag_slow(c.state, c.mbox, c.timeout_ns, f, seq - 1);
+    if (ld_relaxed_sys(f) < need) wait_flag_slow(c.state, c.mbox, c.timeout_ns, f, need);
   }
   __syncthreads();
 }
 
-// End of an LL operation: the last CTA of this rank advances the LL clock and tells every peer
-// that this rank has finished reading operation `seq`.
-__device__ __forceinline__ void ll_finish(const RankCtx& c, u64 seq) {
+// End of an LL operation: the last CTA of this rank advances the LL clock; after a broadcast it
+// also tells every peer that this rank has finished reading it.
+__device__ __forceinline__ void ll_finish(const RankCtx& c, u64 seq, u64 hist, bool bcast) {
   __syncthreads();
   if (threadIdx.x == 0) {
     LocalState* s = c.state;
@@ -238,9 +241,11 @@ __device__ __forceinline__ void ll_finish(const RankCtx& c, u64 seq) {
     if (prev == gridDim.x - 1) {
       s->done = 0;
       s->ll_seq = seq + 1;
+      s->ll_hist = ((hist << 1) & 2) | (bcast ? 1 : 0);
       __threadfence();
-      for (int p = 0; p < c.world; ++p)
-        if (p != c.rank) *reinterpret_cast<volatile u64*>(c.flags[p] + (u64)kLLAckRow * kMaxRanks + c.rank) = seq + 1;
+      if (bcast)
+        for (int p = 0; p < c.world; ++p)
+          if (p != c.rank) *reinterpret_cast<volatile u64*>(c.flags[p] + (u64)kLLAckRow * kMaxRanks + c.rank) = seq + 1;
     }
   }
 }
@@ -253,7 +258,7 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   const RankBufs& ub = pk.buf[ci];
   const int N = c.world, r = c.rank;
   const volatile LocalState* st = c.state;
-  const u64 seq = st->ll_seq;
+  const u64 seq = st->ll_seq, hist = st->ll_hist;
   const u32 flag = (u32)(seq % 0xfffffffeull) + 1u;
   const u64 par = (seq & 1) * (u64)kMaxRanks * kLLSlotBytes;
   const Region src = make_region(ub.send, op.bytes), dst = make_region(ub.recv, op.bytes);
@@ -262,7 +267,7 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   u64 lo, hi;
   block_span(units, units, lo, hi);
   char* my_ll = c.stage[r] + c.ll_off + par;
-  ll_wait_acks(c, seq);
+  ll_wait_acks(c, seq, hist);
   for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
     uint4 v[kMaxRanks];
     const uint4 mine = region_ld(src, als, i);
@@ -310,7 +315,7 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
       if (k < N) R.template add<SUM>(v[k], op.op);
     region_st(dst, ald, i, R.result(op.avg, N));
   }
-  ll_finish(c, seq);
+  ll_finish(c, seq, hist, false);
 }
 
 // broadcast, LL (<= kLLMaxBytes): the root writes {data, flag} packets into its slot of every
@@ -323,7 +328,7 @@ k_broadcast_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   const RankBufs& ub = pk.buf[ci];
   const int N = c.world, r = c.rank, root = op.root;
   const volatile LocalState* st = c.state;
-  const u64 seq = st->ll_seq;
+  const u64 seq = st->ll_seq, hist = st->ll_hist;
   const u32 flag = (u32)(seq % 0xfffffffeull) + 1u;
   const u64 par = (seq & 1) * (u64)kMaxRanks * kLLSlotBytes;
   const Region buf = make_region(ub.recv, op.bytes);
@@ -332,7 +337,7 @@ k_broadcast_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   u64 lo, hi;
   block_span(units, units, lo, hi);
   if (r == root) {
-    ll_wait_acks(c, seq);
+    ll_wait_acks(c, seq, hist);
     for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
       const uint4 mine = region_ld(buf, al, i);
 #pragma unroll
@@ -369,7 +374,7 @@ k_broadcast_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
       region_st(buf, al, i, make_uint4(a.x, a.z, b.x, b.z));
     }
   }
-  ll_finish(c, seq);
+  ll_finish(c, seq, hist, true);
 }
 
 // ---------------------------------------------------------------------------

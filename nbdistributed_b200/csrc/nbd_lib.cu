@@ -690,7 +690,13 @@ static int pipe_launch(const void* fn, int device, int nblocks, int world, bool 
 // copies in an order of its own, so float sums are not bit-identical with the ascending-rank
 // order of every other kernel (they stay within the tolerance of tests/helpers.py and are
 // identical on all ranks).  Broadcast over multicast is a plain copy and needs no opt-in.
-static const u64 kDefNvlsReduceMin = 1ull << 20;
+// Measured at 8xB200 (profiles/r02_bench_n8_mid.json), busbw per rank in GB/s:
+//   staged in-switch pipeline (ordinary buffers): 16 MiB 172, 64 MiB 465, 256 MiB 650, 1 GiB 739
+//   peer-to-peer kernels, same buffers:           16 MiB 327, 64 MiB 508, 256 MiB 577-630, 1 GiB 658
+//   zero-copy in-switch (multicast-pool memory):   1 MiB 76, 16 MiB 445, 64 MiB 632, 256 MiB 772
+//   peer-to-peer zero-copy (symmetric memory):     1 MiB 61, 16 MiB 322, 64 MiB 565, 256 MiB 645
+static const u64 kDefNvlsReduceMin = 128ull << 20;  // staged pipeline
+static const u64 kDefNvlsZcMin = 256ull << 10;      // zero-copy on pool memory
 static const u64 kDefNvlsBcastMin = 512ull << 10;
 
 static bool nvls_reduce_wanted(const nbd_comm* c, u64 bytes, int dtype, int op) {
@@ -698,7 +704,7 @@ static bool nvls_reduce_wanted(const nbd_comm* c, u64 bytes, int dtype, int op) 
   // 326 vs 602 GB/s); from four ranks on it moves less (S(1+1/N) against 2(N-1)/N S)
   return c->nvls.enabled && (c->world > 2 || c->t_nvls_reduce == 2) && !c->t_nvls_off && c->t_nvls_reduce && (op == NBD_SUM || op == NBD_AVG) &&
          (dtype == NBD_F32 || dtype == NBD_BF16 || dtype == NBD_F16) &&
-         bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsReduceMin);
+         bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsZcMin);
 }
 
 // Broadcast over multimem.st is correct but, measured at 8xB200, slower than the scatter kernel at
@@ -730,6 +736,7 @@ static int pipe_all_reduce(nbd_comm* c, const void* send, void* recv, u64 bytes,
   p.op.op = op;
   p.op.avg = (op == NBD_AVG);
   p.op.algo |= mc ? 0 : 1;  // arena staging is shared with the chunked kernels: open with a barrier
+  if (mc && !c->t_pipe_mode) p.op.algo |= 2;  // two reducing groups: 8xB200 256 MiB 712 vs 735 us (profiles/r02_tune2_nvls_diag_n8.jsonl)
   PackPipe<1> pk;
   fill_pipe(pk, c, send, recv, mc);
   c->last_algo = mc ? "ar_nvls" : "ar_pipe";
@@ -951,12 +958,9 @@ static bool auto_wanted(const nbd_comm* c, u64 bytes) {
          bytes >= (c->t_auto_min ? c->t_auto_min : kDefAutoMin);
 }
 
-// all_reduce: at 8 ranks the staged two-shot is already within 3 % of zero-copy (256 MiB: 579 vs
-// 578 GB/s), so the agreement only pays for itself on very large messages; at 4 ranks zero-copy
-// is far ahead (1 GiB: 670 GB/s vs 460 GB/s staged at 256 MiB; profiles/r01_bench_n4_*.json)
-static bool auto_wanted_ar(const nbd_comm* c, u64 bytes) {
-  return auto_wanted(c, bytes) && (c->t_auto_min || c->world <= 4 || bytes >= (512ull << 20));
-}
+// all_reduce takes the same threshold at every world size.  (Round 1 kept 8 ranks staged below
+// 512 MiB on a stale measurement; 8xB200 round 2: 64 MiB staged 493 / auto 507, 256 MiB 577 / 630.)
+static bool auto_wanted_ar(const nbd_comm* c, u64 bytes) { return auto_wanted(c, bytes); }
 
 struct ExportRef {
   u64 slot = kNoSlot;
@@ -1118,7 +1122,7 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
       c->last_algo = "ar_nvls_zerocopy";
       return NBD_OK;
     }
-    return pipe_all_reduce(c, send, recv, bytes, dtype, op, true, s);
+    if (bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsReduceMin)) return pipe_all_reduce(c, send, recv, bytes, dtype, op, true, s);
   }
   if (pipe_wanted(c, bytes)) return pipe_all_reduce(c, send, recv, bytes, dtype, op, false, s);
   if (auto_wanted_ar(c, bytes)) {

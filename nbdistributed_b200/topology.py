@@ -28,15 +28,21 @@ def _nvml_matrix(indices: Sequence[int]) -> Optional[Dict[str, Any]]:
         for i, h in zip(indices, handles):
             name = nv.nvmlDeviceGetName(h)
             pci = nv.nvmlDeviceGetPciInfo(h).busId
-            links = 0
+            links = to_switch = 0
             for link in range(getattr(nv, "NVML_NVLINK_MAX_LINKS", 18)):
                 try:
                     if nv.nvmlDeviceGetNvLinkState(h, link) == nv.NVML_FEATURE_ENABLED:
                         links += 1
+                        try:
+                            if nv.nvmlDeviceGetNvLinkRemoteDeviceType(h, link) == nv.NVML_NVLINK_DEVICE_TYPE_SWITCH:
+                                to_switch += 1
+                        except Exception:
+                            pass
                 except Exception:
                     break
             gpus.append({"index": i, "name": name.decode() if isinstance(name, bytes) else name,
-                         "pci": pci.decode() if isinstance(pci, bytes) else pci, "nvlinks_up": links})
+                         "pci": pci.decode() if isinstance(pci, bytes) else pci, "nvlinks_up": links,
+                         "nvswitch_links": to_switch})
         n = len(indices)
         nvlink = [[a == b for b in range(n)] for a in range(n)]
         p2p = [[a == b for b in range(n)] for a in range(n)]
@@ -52,6 +58,14 @@ def _nvml_matrix(indices: Sequence[int]) -> Optional[Dict[str, Any]]:
                 except Exception:
                     nvlink[a][b] = False
                     p2p[a][b] = False
+                # Found on the 8xB200 box: inside a container nvmlDeviceGetP2PStatus answers "not
+                # supported" for pairs that `nvidia-smi topo -m` shows as NV18 and that CUDA maps
+                # peer to peer.  Two GPUs that both hang off an NVSwitch reach each other over
+                # NVLink; for plain reachability CUDA's own answer is the authority.
+                if not nvlink[a][b] and gpus[a]["nvswitch_links"] > 0 and gpus[b]["nvswitch_links"] > 0:
+                    nvlink[a][b] = True
+                if not p2p[a][b]:
+                    p2p[a][b] = nvlink[a][b] or _cuda_peer(indices[a], indices[b])
         return {"source": "nvml", "gpus": gpus, "p2p": p2p, "nvlink": nvlink}
     finally:
         try:
@@ -60,11 +74,21 @@ def _nvml_matrix(indices: Sequence[int]) -> Optional[Dict[str, Any]]:
             pass
 
 
+def _cuda_peer(a: int, b: int) -> bool:
+    try:
+        import torch
+
+        return bool(torch.cuda.can_device_access_peer(a, b))
+    except Exception:
+        return False
+
+
 def _torch_matrix(indices: Sequence[int]) -> Dict[str, Any]:
     import torch
 
     n = len(indices)
-    gpus = [{"index": i, "name": torch.cuda.get_device_name(i), "pci": None, "nvlinks_up": None} for i in indices]
+    gpus = [{"index": i, "name": torch.cuda.get_device_name(i), "pci": None, "nvlinks_up": None, "nvswitch_links": None}
+            for i in indices]
     p2p = [[a == b or bool(torch.cuda.can_device_access_peer(indices[a], indices[b])) for b in range(n)]
            for a in range(n)]
     return {"source": "torch", "gpus": gpus, "p2p": p2p, "nvlink": None}

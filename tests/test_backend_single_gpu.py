@@ -84,3 +84,28 @@ def test_cuda_only_backend_string_routes_barrier_to_b200():
     p.start()
     p.join(timeout=180)
     assert p.exitcode == 0
+
+
+def test_topology_discovery_on_real_hardware():
+    """topology.discover() through NVML on the GPU box (the fake-matrix CPU test covers the logic):
+    square matrix over every visible GPU, every pair reachable peer to peer on an NVSwitch box,
+    and check_assignment accepts one rank per GPU (ref:src/nbdistributed/process_manager.py:104-115
+    assigns GPUs blindly)."""
+    import torch
+
+    from nbdistributed_b200 import topology
+
+    n = torch.cuda.device_count()
+    topo = topology.discover()
+    assert topo["source"] == "nvml", topo["source"]  # pynvml ships in the image: no torch fallback needed
+    assert len(topo["gpus"]) == n and len(topo["p2p"]) == n and all(len(row) == n for row in topo["p2p"])
+    assert all("B200" in g["name"] for g in topo["gpus"]), [g["name"] for g in topo["gpus"]]
+    assert all(g["nvlinks_up"] == 18 for g in topo["gpus"]), [g["nvlinks_up"] for g in topo["gpus"]]
+    if n >= 2:
+        assert topo["all_p2p"] and topo["all_nvlink"], topology.format_matrix(topo)
+    rep = topology.check_assignment(n, list(range(n)), topo=topo)
+    assert rep["map"] == list(range(n)) and rep["warnings"] == []
+    text = topology.format_matrix(topo)
+    assert "GPU0" in text and "source: nvml" in text
+    with pytest.raises(ValueError):
+        topology.check_assignment(2, [0, 0], topo=topo)  # two ranks on one GPU

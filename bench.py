@@ -292,6 +292,25 @@ def run_ours_single(args):
     torch.cuda.synchronize()
     e2e_ms = max(ev0.elapsed_time(ev1), (time.perf_counter() - t0) * 1e3) / e2e_steps
     e2e_value = S * bus_factor(R) * R / (e2e_ms * 1e-3) / 1e9
+    # ceiling of that leg: the same pinned H2D + D2H bytes with no collective in between
+    d_in = [torch.empty_like(s) for s in sends[:2]]
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def copies_only():
+        for r in range(R):
+            with torch.cuda.stream(s1):
+                d_in[r % 2].copy_(host_in[r], non_blocking=True)
+            with torch.cuda.stream(s2):
+                host_out[r].copy_(recvs[r], non_blocking=True)
+
+    copies_only()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        copies_only()
+    torch.cuda.synchronize()
+    ceiling_ms = (time.perf_counter() - t0) * 1e3 / 3
+    del d_in
 
     # ---- roofline of the dominant kernel (the all_reduce launch itself) ------------------
     peak, peak_src = measured_hbm_peak()
@@ -318,7 +337,9 @@ def run_ours_single(args):
                    "value_definition": "sum over ranks of S*2(R-1)/R bytes per second"},
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": R * S, "d2h_bytes_per_step": R * S,
-                "ms_per_step": round(e2e_ms, 3), "api": "nbd_emu_all_reduce_host (pinned host buffers in, pinned host buffers out; chunked H2D/collective/D2H "
+                "ms_per_step": round(e2e_ms, 3), "host_copy_only_ms": round(ceiling_ms, 3),
+                "frac_of_host_copy_ceiling": round(ceiling_ms / e2e_ms, 3),
+                "api": "nbd_emu_all_reduce_host (pinned host buffers in, pinned host buffers out; chunked H2D/collective/D2H "
                        "pipeline inside the call)"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
@@ -527,6 +548,56 @@ def parity_check(torch, dist, dev, rank, world, cpu_group, be, B):
 
 
 
+def bind_near_gpu(physical_index: int):
+    """Run this process on the CPUs NVML names as closest to its GPU, so that the pinned host
+    buffers of the end-to-end leg are allocated on that NUMA node.  Returns how many CPUs."""
+    try:
+        import pynvml as nv
+
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(physical_index)
+        ncpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
+def host_copy_ceiling(torch, dist, dev, cpu_group, nbytes, iters=4):
+    """What the box gives every GPU at once for pinned H2D + D2H of `nbytes` each way with NO
+    collective in between: the ceiling of the end-to-end leg (one cudaMemcpyAsync per copy, two
+    streams per rank, all ranks concurrently; ms per step, max over ranks)."""
+    h_in = torch.empty(nbytes // 4, dtype=torch.float32).pin_memory()
+    h_out = torch.empty(nbytes // 4, dtype=torch.float32).pin_memory()
+    d_in = torch.empty(nbytes // 4, dtype=torch.float32, device=dev)
+    d_out = torch.zeros(nbytes // 4, dtype=torch.float32, device=dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def step():
+        with torch.cuda.stream(s1):
+            d_in.copy_(h_in, non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_out.copy_(d_out, non_blocking=True)
+
+    step()
+    torch.cuda.synchronize()
+    dist.barrier(group=cpu_group)
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        step()
+    torch.cuda.synchronize()
+    t = torch.tensor([(time.perf_counter() - t0) * 1e3 / iters], dtype=torch.float64)
+    dist.barrier(group=cpu_group)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=cpu_group)
+    del h_in, h_out, d_in, d_out
+    return float(t.item())
+
+
 def run_ours_multi(args):
     import torch
     import torch.distributed as dist
@@ -536,6 +607,7 @@ def run_ours_multi(args):
 
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
+    bound_cpus = bind_near_gpu(physical_gpu_index(local))
     ns = W.init_worker(rank, world, os.environ.get("MASTER_ADDR", "127.0.0.1"), os.environ.get("MASTER_PORT", "29500"),
                        gpu_id=local, backend="b200")
     os.environ["LOCAL_RANK"] = str(local)
@@ -548,6 +620,12 @@ def run_ours_multi(args):
     src = torch.randn(numel, generator=g, device=dev, dtype=torch.float32) * 0.01
     x = src.clone()
     be = B.get_backend()
+    # first collective = lazy communicator set-up (arena, CUDA-IPC exchange over the store, NVSwitch
+    # multicast rendezvous): what lengthens the reference's fixed 2 s start-up wait
+    t_init = time.perf_counter()
+    dist.all_reduce(torch.zeros(256, device=dev))
+    torch.cuda.synchronize()
+    init_ms = (time.perf_counter() - t_init) * 1e3
 
     def step():
         dist.all_reduce(x)
@@ -634,6 +712,7 @@ def run_ours_multi(args):
     log(f"timed region done: {ms:.3f} ms/step, busbw/rank {per_rank:.1f} GB/s; measuring e2e")
     e2e_ms = _time_collective(torch, dist, e2e_step, max(2, min(args.steps, 5)), 1, cpu_group)
     e2e_per_rank = S * bus_factor(world) / (e2e_ms * 1e-3) / 1e9
+    ceiling_ms = host_copy_ceiling(torch, dist, dev, cpu_group, S)
 
     extras = {}
     if nvls_on:
@@ -679,10 +758,15 @@ def run_ours_multi(args):
             "clocks": clocks,
             "e2e": {"value": round(e2e_per_rank * world, 2), "unit": UNIT, "h2d_bytes_per_step": S * world,
                     "d2h_bytes_per_step": S * world, "ms_per_step": round(e2e_ms, 3),
+                    "host_copy_only_ms": round(ceiling_ms, 3), "frac_of_host_copy_ceiling": round(ceiling_ms / e2e_ms, 3),
+                    "ceiling_note": "host_copy_only_ms = the same pinned H2D + D2H on every GPU at once with no collective "
+                                    "(what this box's PCIe/host memory gives); the end-to-end step cannot beat it",
+                    "cpus_bound_near_gpu": bound_cpus,
                     "api": "nbdistributed_b200.backend.all_reduce_host (BackendB200 -> nbd_all_reduce_host): pinned host "
                            "buffers in and out, chunked H2D/collective/D2H pipeline inside the call"},
             "gpu_launches": int(launches),
             "parity_check": pc,
+            "communicator_init_ms": round(init_ms, 1),
             "roofline": {"bound": "nvlink", "achieved": round(per_rank, 1), "peak": NVLINK_PEAK_GBS, "unit": "GB/s",
                          "frac": round(per_rank / NVLINK_PEAK_GBS, 4),
                          "traffic": (nvlink["tx_bytes_per_step"] + nvlink["rx_bytes_per_step"]) if nvlink else None,

@@ -291,7 +291,14 @@ int nbd_emu_all_reduce_host(nbd_comm_t any, const void* const* host_sends, void*
  *  - the first call on a device looks up the array's device address; make that first call
  *    before starting any stream capture on that device;
  *  - all calls share the one array: order them on the GPU (same stream, or events).  Calls
- *    whose device work overlaps race on it and produce wrong results. */
+ *    whose device work overlaps race on it and produce wrong results;
+ *  - the first call on a device also makes the CUDA runtime load this library's module and the
+ *    kernel (driver-side memory the caller does not see): treat it as a warm-up;
+ *  - there is no communicator, hence no asynchronous error channel: the flag-wait watchdog (10 s)
+ *    of this entry point writes its verdict into the scratch array, which the host never reads.
+ *    All ranks run inside ONE cooperative launch, so a wait can only time out if the GPU itself
+ *    is wedged; the call's return value reports argument and launch errors only;
+ *  - sends/recvs must be device pointers of the CURRENT device (not checked). */
 #define NBD_NOALLOC_MAX_BYTES (1u << 20)
 int nbd_local_all_reduce_noalloc(const void* const* sends, void* const* recvs, int world_size,
                                  size_t count, int dtype, int op, void* stream);

@@ -51,3 +51,15 @@ def test_hot_kernels_keep_their_register_and_spill_budget(native_lib):
             # 128 registers = one 512-thread CTA per SM, which the grid cap (SM count) relies on
             assert regs <= max_regs, (frag, regs)
             assert stack <= max_stack, f"{frag}: {stack} bytes of local stack (budget {max_stack}): spills in a hot loop"
+
+
+def test_product_library_holds_tma_and_multimem_code(native_lib):
+    """The tile pipeline's copy phases are bulk async copies (TMA: UBLKCP in SASS) and its
+    NVSwitch transport is multimem.ld_reduce (LDGMC in SASS) - in the shipped library, not in a
+    probe tool."""
+    from nbdistributed_b200 import capi
+
+    sass = _run("-sass", capi.LIB_PATH)
+    assert sass.count("UBLKCP") >= 50, sass.count("UBLKCP")
+    assert "LDGMC.E.ADD.F32x4" in sass and "LDGMC.E.HPADD.BF16x8" in sass
+    assert "SYNCS.ARRIVE.TRANS64" in sass  # mbarrier expect_tx of the TMA rings

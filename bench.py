@@ -206,6 +206,24 @@ def cpu_baseline_object(ranks: int, msg_bytes: int):
     }
 
 
+def configs_cpu_baseline(ranks: int, configs: dict) -> None:
+    """The reference's gloo path on the same two workloads, one pass each on the host cores
+    (config 3: 149 broadcasts; config 4: 77 bf16 all_reduces); fills `gloo_ms` into `configs`."""
+    from oracle.gloo_runner import time_gloo
+
+    try:
+        jobs = [{"kind": "broadcast", "dtype": "f32", "numel": n, "iters": 1, "warmup": 0, "root": 0} for n in gpt2_small_numels()]
+        t3 = sum(time_gloo(ranks, jobs, timeout=240.0))
+        configs["cfg3_gpt2_state_dict_broadcast"]["gloo_ms"] = round(t3 * 1e3, 1)
+        jobs = [{"kind": "all_reduce", "dtype": "bf16", "numel": n, "iters": 1, "warmup": 0} for n in ddp_bucket_numels()]
+        t4 = sum(time_gloo(ranks, jobs, timeout=300.0))
+        configs["cfg4_ddp_bf16_gradient_all_reduce"]["gloo_ms"] = round(t4 * 1e3, 1)
+        configs["gloo_note"] = (f"gloo, {ranks} local processes on {os.cpu_count()} host cores, one pass per tensor "
+                                "(barrier-fenced per tensor, summed)")
+    except Exception as e:  # noqa: BLE001 - the bench line must still be printed
+        configs["gloo_note"] = f"gloo baseline failed: {str(e)[:160]}"
+
+
 def _torch_version():
     import torch
 
@@ -738,6 +756,9 @@ def run_ours_multi(args):
         extras["latency"] = kernel_latency(torch, dist, dev, world, cpu_group, be)
         log("registered-memory sweep")
         extras["registered"] = registered_sweep(torch, dist, dev, world, cpu_group, be)
+    if not args.no_sweep:
+        log("BASELINE configs 3 and 4")
+        extras["configs"] = model_configs(torch, dist, dev, rank, world, cpu_group)
     if not args.no_nccl:
         log("NCCL comparison point")
         extras["nccl"] = nccl_comparison(torch, dist, dev, world, cpu_group, S)
@@ -784,6 +805,8 @@ def run_ours_multi(args):
     if rank == 0 and not args.no_cpu_baseline:
         log("gloo CPU baseline")
         line["cpu_baseline"] = cpu_baseline_object(world, S)
+        if "configs" in line:
+            configs_cpu_baseline(world, line["configs"])
     return line
 
 
@@ -810,6 +833,80 @@ def registered_sweep(torch, dist, dev, world, cpu_group, be):
         out.append({"op": name, "dtype": "bfloat16", "bytes": 1 << 30, "us": round(ms * 1e3, 2),
                     "busbw_per_rank": round((1 << 30) * (world - 1) / world / (ms * 1e-3) / 1e9, 2), "algo": be.last_algo()})
     del flat, big
+    return out
+
+
+def gpt2_small_numels():
+    """Element counts of GPT2LMHeadModel(GPT2Config()).state_dict() incl. the tied lm_head alias
+    (149 tensors, BASELINE config 3; pinned by tests/test_configs_shapes.py)."""
+    d, v, p, layers = 768, 50257, 1024, 12
+    n = [v * d, p * d]
+    for _ in range(layers):
+        n += [d, d, d * 3 * d, 3 * d, d * d, d, d, d, d * 4 * d, 4 * d, 4 * d * d, d]
+    return n + [d, d, v * d]
+
+
+def ddp_bucket_numels():
+    """bf16 gradient buckets of the 1.236 G-parameter Llama-style model of BASELINE config 4:
+    the tied embedding, DDP's 1 MiB first bucket, then 25 MiB buckets."""
+    params, emb = 1_235_814_400, 128256 * 2048
+    sizes = [emb, (1 << 20) // 2]
+    rest, cap = params - sum(sizes), (25 << 20) // 2
+    while rest > 0:
+        sizes.append(min(cap, rest))
+        rest -= sizes[-1]
+    return sizes
+
+
+def model_configs(torch, dist, dev, rank, world, cpu_group):
+    """BASELINE configs 3 and 4 through dist.* on backend b200 (checked, then timed).  The gloo
+    figures beside them are added on rank 0 after the GPUs are released (configs_cpu_baseline)."""
+    out = {}
+    tensors = [(torch.randn(n, device=dev) if rank == 0 else torch.zeros(n, device=dev)) for n in gpt2_small_numels()]
+    total = sum(t.numel() * 4 for t in tensors)
+
+    def per_tensor():
+        for t in tensors:
+            dist.broadcast(t, src=0)
+
+    def coalesced():
+        with dist._coalescing_manager(device=dev):
+            for t in tensors:
+                dist.broadcast(t, src=0)
+
+    per_tensor()
+    torch.cuda.synchronize()
+    chk = torch.stack([t.view(torch.int32).sum(dtype=torch.int64) for t in tensors]).cpu()
+    allc = [torch.empty_like(chk) for _ in range(world)]
+    dist.all_gather(allc, chk, group=cpu_group)
+    ok = all(torch.equal(a, allc[0]) for a in allc)
+    ms_a = _time_collective(torch, dist, per_tensor, 5, 1, cpu_group)
+    ms_b = _time_collective(torch, dist, coalesced, 5, 1, cpu_group)
+    out["cfg3_gpt2_state_dict_broadcast"] = {
+        "tensors": len(tensors), "bytes": total, "identical_on_all_ranks": ok,
+        "ms_per_tensor_loop": round(ms_a, 3), "ms_in_coalescing_block": round(ms_b, 3),
+        "effective_GBps": round(total / min(ms_a, ms_b) / 1e6, 1)}
+    del tensors
+    buckets = [torch.full((n,), float(rank + 1), device=dev, dtype=torch.bfloat16) for n in ddp_bucket_numels()]
+
+    def ddp_step():
+        works = [dist.all_reduce(b, async_op=True) for b in reversed(buckets)]
+        for w in works:
+            w.wait()
+
+    ddp_step()
+    torch.cuda.synchronize()
+    want = float(world * (world + 1) // 2)
+    ok4 = all(bool((b[:: max(1, b.numel() // 1000)] == want).all()) for b in buckets)
+    for b in buckets:
+        b.fill_(0.001)
+    ms4 = _time_collective(torch, dist, ddp_step, 5, 2, cpu_group)
+    nbytes4 = sum(b.numel() for b in buckets) * 2
+    out["cfg4_ddp_bf16_gradient_all_reduce"] = {
+        "buckets": len(buckets), "bytes": nbytes4, "exact": ok4, "ms_per_step": round(ms4, 3),
+        "busbw_per_rank": round(nbytes4 * bus_factor(world) / ms4 / 1e6, 1)}
+    del buckets
+    torch.cuda.empty_cache()
     return out
 
 
@@ -855,7 +952,7 @@ def multi_sweep(torch, dist, dev, world, cpu_group, be, only_all_reduce=False):
         del flat, shard
     for kind in (("all_reduce",) if only_all_reduce else ("all_reduce", "broadcast")):
         for dt, es in ((torch.float32, 4), (torch.bfloat16, 2)):
-            for nbytes in (4 << 10, 64 << 10, 1 << 20, 16 << 20, 64 << 20, 256 << 20, 1 << 30):
+            for nbytes in [1 << k for k in range(12, 31)]:  # BASELINE config 2: 4 KB ... 1 GB, 19 sizes
                 if only_all_reduce and nbytes < (1 << 20):
                     continue
                 if dt == torch.bfloat16 and nbytes not in (4 << 10, 1 << 20, 64 << 20, 1 << 30):

@@ -747,7 +747,7 @@ def run_ours_multi(args):
         extras["sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be)
         if nvls_on:
             log("in-switch reduction sweep")
-            be.set_tunable("nvls_reduce", 1)
+            be.set_tunable("nvls_reduce", 2)  # 2: measure the switch path at any world size (the default policy uses it beyond 4 ranks)
             extras["nvls_sweep"] = multi_sweep(torch, dist, dev, world, cpu_group, be, only_all_reduce=True)
             log("in-switch reduction on multicast-pool memory (zero copy)")
             extras["nvls_registered"] = nvls_registered_sweep(torch, dist, dev, world, cpu_group, be)

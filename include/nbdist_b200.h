@@ -136,8 +136,8 @@ int nbd_comm_get_tunable(nbd_comm_t comm, const char* name, uint64_t* value);
  *   - nbd_broadcast of >= 512 KiB writes each tile once (multimem.st; the switch replicates it);
  *   - nbd_all_reduce of f32/bf16/f16 SUM/AVG of >= 1 MiB is reduced INSIDE the switch
  *     (multimem.ld_reduce) when the tunable "nvls_reduce" is 1 (or NBDIST_B200_NVLS_REDUCE=1)
- *     and the group has more than two ranks (2 forces it for two ranks as well, where the
- *     peer-to-peer kernels are faster); while it is on, nbd_mem_alloc hands out memory from a
+ *     and the group has more than four ranks (2 forces it for smaller groups as well, where
+ *     the peer-to-peer kernels measured faster); while it is on, nbd_mem_alloc hands out memory from a
  *     pool bound into the multicast object (NBDIST_B200_NVLS_POOL_BYTES, default 1 GiB) and
  *     all_reduce on such memory runs without any staging.
  *     Opt-in because the switch adds in an order of its own: results are identical on all ranks

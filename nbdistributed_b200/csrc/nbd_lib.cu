@@ -699,10 +699,17 @@ static const u64 kDefNvlsReduceMin = 128ull << 20;  // staged pipeline
 static const u64 kDefNvlsZcMin = 256ull << 10;      // zero-copy on pool memory
 static const u64 kDefNvlsBcastMin = 512ull << 10;
 
+// In-switch float sums pay from more than four ranks on.  Wire bytes per GPU and direction are
+// S(1 + 1/N) through the switch against 2(N-1)/N S peer to peer: a loss at two ranks (326 against
+// 602 GB/s), and at four the smaller saving is eaten by the switch path's lower efficiency
+// (4xB200, 256 MiB: staged 562 / pool 645 against 636 / 657 peer to peer; profiles/r02_bench_n4.json);
+// at eight: 654-660 / 772 against 630 / 645.  "nvls_reduce" = 2 forces it at any world size.
+static bool nvls_reduce_policy(const nbd_comm* c) {
+  return c->nvls.enabled && !c->t_nvls_off && c->t_nvls_reduce && (c->world > 4 || c->t_nvls_reduce == 2);
+}
+
 static bool nvls_reduce_wanted(const nbd_comm* c, u64 bytes, int dtype, int op) {
-  // two ranks: the switch path moves 1.5 S per direction against S peer to peer (2xB200, 256 MiB:
-  // 326 vs 602 GB/s); from four ranks on it moves less (S(1+1/N) against 2(N-1)/N S)
-  return c->nvls.enabled && (c->world > 2 || c->t_nvls_reduce == 2) && !c->t_nvls_off && c->t_nvls_reduce && (op == NBD_SUM || op == NBD_AVG) &&
+  return nvls_reduce_policy(c) && (op == NBD_SUM || op == NBD_AVG) &&
          (dtype == NBD_F32 || dtype == NBD_BF16 || dtype == NBD_F16) &&
          bytes >= (c->t_nvls_min ? c->t_nvls_min : kDefNvlsZcMin);
 }
@@ -1904,7 +1911,7 @@ extern "C" int nbd_mem_alloc(nbd_comm_t c, size_t bytes, void** ptr, void* handl
   if (bytes == 0) return fail(NBD_ERR_INVALID_ARGUMENT, "cannot allocate 0 bytes");
   DeviceGuard g(c->device);
   const size_t rounded = (bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
-  if (c->nvls.enabled && c->t_nvls_reduce && !c->t_nvls_off) {
+  if (nvls_reduce_policy(c)) {
     // In-switch reduction is on: hand out memory that is bound into the multicast object, so
     // that all_reduce on it needs no staging.  Peers do not map it (multimem.* reaches every
     // copy through the switch); every other collective treats it as an ordinary buffer.

@@ -1122,7 +1122,10 @@ int nbd_all_reduce(nbd_comm_t c, const void* send, void* recv, size_t count, int
       fill_pack(pk, c, send, recv);
       McPtrs m = {c->regs[ks].mc + offs, c->regs[kr].mc + offr};
       OpParams prm = zc_params(c, bytes, op, 0);
-      const int nb = pick_blocks(c, ceil_div(bytes / kUnit, (u64)c->world), 0);
+      // 32 CTAs saturate the switch path and leave fewer flags to exchange at the two barriers:
+      // 8xB200, 256 MiB: 800 GB/s with 32, 789 with 64, 764 with 148 (profiles/r02_tune3_n8.jsonl)
+      int nb = pick_blocks(c, ceil_div(bytes / kUnit, (u64)c->world), 0);
+      if (!c->t_blocks && nb > 32) nb = 32;
       void* args[3] = {(void*)&pk, (void*)&m, (void*)&prm};
       NBD_CUDA(cudaLaunchKernel(fn, dim3(nb, 1, 1), dim3(kThreads, 1, 1), args, 0, s));
       g_launches.fetch_add(1);

@@ -8,6 +8,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdarg.h>
+#include <stddef.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -1001,9 +1002,17 @@ static ExportRef export_ref(nbd_comm* c, const void* ptr, u64 bytes, cudaStream_
     e.base = (u64)base;
     e.size = (u64)size;
     memcpy(e.ipc, &h, sizeof(h));
-    e.valid = 1;
+    // The record first, its `valid` word last and in a copy of its own: a peer's host reads the
+    // slot with a device-to-host copy that may run while ours is in flight, and must never see
+    // valid == 1 on a half-written record.  (Both copies are ordered on `s`; the 1 comes from a
+    // pinned cell of its own because the mirror is read when the copy executes, not when it is
+    // enqueued.)
+    e.valid = 0;
     char* row = c->arena + (size_t)(kExportRow0 + c->n_exports * kExportSlotRows) * kMaxRanks * sizeof(u64);
-    if (cudaMemcpyAsync(row, &e, sizeof(e), cudaMemcpyHostToDevice, s) != cudaSuccess) {
+    uint64_t* one = &c->imp_tmp[c->imp_tmp_n++ % 64];
+    *one = 1;
+    if (cudaMemcpyAsync(row, &e, sizeof(e), cudaMemcpyHostToDevice, s) != cudaSuccess ||
+        cudaMemcpyAsync(row + offsetof(ExportSlot, valid), one, sizeof(uint64_t), cudaMemcpyHostToDevice, s) != cudaSuccess) {
       cudaGetLastError();
       return ref;
     }

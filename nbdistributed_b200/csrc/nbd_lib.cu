@@ -910,7 +910,9 @@ static OpParams zc_params(const nbd_comm* c, u64 bytes, int op, int algo) {
 
 // all_reduce zero-copy variant: fused loop for two ranks, tiled read-then-push beyond
 static void zc_ar_variant(const nbd_comm* c, OpParams* p) {
-  const bool tiled = c->t_zc_fused ? (c->t_zc_fused == 2) : (c->world > 2);
+  // Emulated ranks (every "peer" is local HBM) always take the fused loop: the tile's re-read
+  // buys nothing without NVLink (1 GPU, 8 x 256 MiB: 0.731 ms fused against 0.789 tiled).
+  const bool tiled = c->t_zc_fused ? (c->t_zc_fused == 2) : (c->world > 2 && !c->emu);
   p->algo = tiled ? 1 : 0;
   p->chunk_bytes = tiled ? c->t_zc_tile : 0;
 }
@@ -1389,8 +1391,15 @@ int nbd_emu_all_reduce(nbd_comm_t any, const void* const* sends, void* const* re
     OpParams prm = zc_params(c0, bytes, op, 0);
     zc_ar_variant(c0, &prm);
     set_algo(c0, "ar_zerocopy");
-    return launch_zc_reduce<kMaxRanks>(Z_AR, dtype, op, pick_blocks(c0, ceil_div(ceil_div(bytes, kUnit), g->world), g->world),
-                                       g->world, s, zk, &prm);
+    // grid per rank: the largest power of two that fits (8 ranks on 148 SMs: 16 CTAs each, 0.697 ms
+    // against 0.734 with 18; profiles/r02_tune_emu_n1.jsonl)
+    int nb = pick_blocks(c0, ceil_div(ceil_div(bytes, kUnit), g->world), g->world);
+    if (!c0->t_blocks) {
+      int p2 = 1;
+      while (p2 * 2 <= nb) p2 *= 2;
+      nb = p2;
+    }
+    return launch_zc_reduce<kMaxRanks>(Z_AR, dtype, op, nb, g->world, s, zk, &prm);
   }
   Pack<kMaxRanks> pk;
   if ((rc = fill_pack_emu(pk, g, sends, recvs)) != NBD_OK) return rc;

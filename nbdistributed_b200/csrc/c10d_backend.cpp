@@ -39,8 +39,6 @@
 namespace {
 
 constexpr const char* kBackendName = "b200";
-// broadcasts up to this size issued inside a coalescing block are packed into one table launch
-constexpr size_t kCoalesceMaxBytes = 256u << 10;
 
 bool debug_on() {
   static const bool on = [] { const char* e = std::getenv("NBDIST_B200_DEBUG"); return e && e[0] != '0'; }();
@@ -285,7 +283,7 @@ class BackendB200 : public c10d::Backend {
     const int root = (int)opts.rootRank;
     {
       std::lock_guard<std::mutex> lk(mu_);
-      if (coalescing_ && (size_t)t.nbytes() <= kCoalesceMaxBytes) {  // small: one table launch at endCoalescing
+      if (coalescing_) {  // collected: endCoalescing runs the block's broadcasts as tables (nbd_broadcast_table)
         co_bcast_.push_back({t, root});
         co_tensors_.push_back(t);
         return collected_work(t);
@@ -446,7 +444,8 @@ class BackendB200 : public c10d::Backend {
 
   // dist.batch_isend_irecv and `with dist._coalescing_manager(group, device)`: point-to-point
   // operations issued in between are collected and run as ONE batch (so their relative order
-  // on different ranks cannot deadlock); small broadcasts are collected into one table launch.
+  // on different ranks cannot deadlock); broadcasts are collected into table launches (small ones
+  // one direct push, a state_dict's worth of same-root tensors one scatter pipeline).
   void startCoalescing() override {
     std::lock_guard<std::mutex> lk(mu_);
     TORCH_CHECK(!coalescing_, "[b200] startCoalescing called twice");

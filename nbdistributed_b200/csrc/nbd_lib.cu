@@ -1525,10 +1525,34 @@ int nbd_emu_barrier(nbd_comm_t any, void* stream) {
 // ---------------------------------------------------------------------------
 namespace {
 
-// Launches items [i0, i1) as one table.  bufs[r][k]: rank r's buffer of item k (real rank: r = 0).
+// Chunking of a flat table (k_bcast_flat): the packed table is one message of `bytes`, every
+// chunk is cut into N-1 shards that must each fit one staging half.
+static Plan plan_flat(nbd_comm* c, u64 bytes, int root, int emu_world) {
+  Plan p;
+  memset(&p, 0, sizeof(p));
+  const u64 nsh = (u64)(c->world - 1);
+  p.op.bytes = bytes;
+  p.op.root = root;
+  p.op.world = c->world;
+  p.op.algo = 1;
+  const u64 cap = floor_to((c->ctx.half_bytes - kUnit) * nsh, (u64)kUnit * nsh);
+  u64 chunk = c->t_chunk ? floor_to(c->t_chunk, (u64)kUnit * nsh) : floor_to(kDefChunkBcast, (u64)kUnit * nsh);
+  if (chunk < (u64)kUnit * nsh) chunk = (u64)kUnit * nsh;
+  if (chunk > cap) chunk = cap;
+  chunk = fit_chunk(chunk, bytes, (u64)kUnit * nsh);
+  p.op.chunk_bytes = chunk;
+  p.op.nchunks = (u32)ceil_div(bytes, chunk);
+  p.nblocks = pick_blocks(c, ceil_div(ceil_div(chunk, kUnit), nsh), emu_world);
+  return p;
+}
+
+// Launches items [i0, i1) as one table.  items[r][k]: rank r's view of item k (real rank: r = 0).
+// flat: the scatter pipeline over the packed table (all items share one root), any size;
+// otherwise the direct push, whose packed size must fit one staging half.
 template <int NCTX>
-int launch_table(nbd_comm* c0, const RankCtx* ctx, int world, const nbd_bcast_item* const* items, int i0, int i1, cudaStream_t s) {
-  static thread_local PackTable<NCTX> pk;  // ~10 KiB: keep it off the stack
+int launch_table(nbd_comm* c0, const RankCtx* ctx, int world, const nbd_bcast_item* const* items, int i0, int i1, bool flat,
+                 cudaStream_t s) {
+  static thread_local PackTable<NCTX> pk;  // 5-22 KiB: keep it off the stack
   memset(&pk, 0, sizeof(pk));
   for (int r = 0; r < NCTX && r < world; ++r) pk.ctx[r] = ctx[r];
   u64 units = 0;
@@ -1540,46 +1564,76 @@ int launch_table(nbd_comm* c0, const RankCtx* ctx, int world, const nbd_bcast_it
     for (int r = 0; r < NCTX && r < world; ++r) pk.buf[r][j] = (char*)items[r][k].buf;
     units += ceil_div((u64)items[0][k].bytes, kUnit);
   }
+  if (units > 0xffffffffull) return fail(NBD_ERR_INVALID_ARGUMENT, "broadcast table of %llu bytes: more than 64 GiB", (unsigned long long)(units * kUnit));
   pk.d.nitems = i1 - i0;
   pk.d.first[pk.d.nitems] = (u32)units;
-  const int nblocks = pick_blocks(c0, units, NCTX == 1 ? 0 : world);
-  void* args[1] = {(void*)&pk};
-  if (NCTX == 1) {
-    NBD_CUDA(cudaLaunchKernel((const void*)k_bcast_table<NCTX>, dim3(nblocks, 1, 1), dim3(kThreads, 1, 1), args, 0, s));
+  const int emu_world = NCTX == 1 ? 0 : world;
+  Plan p;
+  memset(&p, 0, sizeof(p));
+  const void* fn;
+  void* args[2] = {(void*)&pk, (void*)&p.op};  // k_bcast_table takes the first only
+  if (flat) {
+    p = plan_flat(c0, units * kUnit, items[0][i0].root, emu_world);
+    fn = (const void*)k_bcast_flat<NCTX>;
   } else {
-    NBD_CUDA(cudaLaunchCooperativeKernel((const void*)k_bcast_table<NCTX>, dim3(nblocks, world, 1), dim3(kThreads, 1, 1), args, 0, s));
+    p.nblocks = pick_blocks(c0, units, emu_world);
+    fn = (const void*)k_bcast_table<NCTX>;
+  }
+  if (NCTX == 1) {
+    NBD_CUDA(cudaLaunchKernel(fn, dim3(p.nblocks, 1, 1), dim3(kThreads, 1, 1), args, 0, s));
+  } else {
+    NBD_CUDA(cudaLaunchCooperativeKernel(fn, dim3(p.nblocks, world, 1), dim3(kThreads, 1, 1), args, 0, s));
   }
   g_launches.fetch_add(1);
   return NBD_OK;
 }
 
-// Cuts the item list into tables (<= kTableMax items, packed size <= one staging half); an item
-// too large for a table is handed to `big` (the ordinary broadcast).
+// A table beyond this size whose items share one root runs as a flat table (scatter pipeline);
+// the direct push of the small table would make the root send (N-1) copies of it.
+static const u64 kFlatMinBytes = 256ull << 10;
+
+// Cuts the item list into launches.  The list is taken kTableMax items at a time; a run whose
+// items share a root and together exceed kFlatMinBytes is one flat table.  Any other run is cut
+// into direct-push tables (packed size <= one staging half), and an item too large for one of
+// those is handed to `big` (the ordinary broadcast).  table(i0, i1, flat) launches items [i0, i1).
 template <typename Table, typename Big>
-int run_tables(const nbd_comm* c0, const nbd_bcast_item* items, int n, int world, Table table, Big big) {
+int run_tables(const nbd_comm* c0, const nbd_bcast_item* items, int n, Table table, Big big) {
   const u64 cap_units = c0->ctx.half_bytes / kUnit;
-  int i0 = 0;
-  u64 units = 0;
-  for (int k = 0; k <= n; ++k) {
-    const u64 u = k < n ? ceil_div((u64)items[k].bytes, kUnit) : 0;
-    const bool oversize = k < n && u > cap_units / 2;
-    if (k == n || oversize || k - i0 == kTableMax || units + u > cap_units) {
-      if (k > i0) {
-        int rc = table(i0, k);
-        if (rc != NBD_OK) return rc;
-      }
-      i0 = k;
-      units = 0;
-      if (oversize) {
-        int rc = big(k);
-        if (rc != NBD_OK) return rc;
-        i0 = k + 1;
-        continue;
-      }
+  for (int a = 0; a < n; a += kTableMax) {
+    const int b = a + kTableMax < n ? a + kTableMax : n;
+    bool one_root = true;
+    u64 total = 0;
+    for (int k = a; k < b; ++k) {
+      one_root = one_root && items[k].root == items[a].root;
+      total += (u64)items[k].bytes;
     }
-    units += u;
+    if (one_root && total > kFlatMinBytes) {
+      int rc = table(a, b, true);
+      if (rc != NBD_OK) return rc;
+      continue;
+    }
+    int i0 = a;
+    u64 units = 0;
+    for (int k = a; k <= b; ++k) {
+      const u64 u = k < b ? ceil_div((u64)items[k].bytes, kUnit) : 0;
+      const bool oversize = k < b && u > cap_units / 2;
+      if (k == b || oversize || units + u > cap_units) {
+        if (k > i0) {
+          int rc = table(i0, k, false);
+          if (rc != NBD_OK) return rc;
+        }
+        i0 = k;
+        units = 0;
+        if (oversize) {
+          int rc = big(k);
+          if (rc != NBD_OK) return rc;
+          i0 = k + 1;
+          continue;
+        }
+      }
+      units += u;
+    }
   }
-  (void)world;
   return NBD_OK;
 }
 
@@ -1605,11 +1659,15 @@ extern "C" int nbd_broadcast_table(nbd_comm_t c, const nbd_bcast_item* items, in
   for (int k = 0; k < n; ++k)
     if (items[k].bytes) live.push_back(items[k]);
   const nbd_bcast_item* rows[1] = {live.data()};
+  bool flat_seen = false;
   rc = run_tables(
-      c, live.data(), (int)live.size(), c->world,
-      [&](int i0, int i1) { return launch_table<1>(c, &c->ctx, c->world, rows, i0, i1, (cudaStream_t)stream); },
+      c, live.data(), (int)live.size(),
+      [&](int i0, int i1, bool flat) {
+        flat_seen = flat_seen || flat;
+        return launch_table<1>(c, &c->ctx, c->world, rows, i0, i1, flat, (cudaStream_t)stream);
+      },
       [&](int k) { return nbd_broadcast(c, live[(size_t)k].buf, live[(size_t)k].bytes, NBD_BYTES, live[(size_t)k].root, stream); });
-  c->last_algo = "bcast_table";
+  c->last_algo = flat_seen ? "bcast_flat" : "bcast_table";
   return rc;
 }
 
@@ -1641,15 +1699,19 @@ extern "C" int nbd_emu_broadcast_table(nbd_comm_t any, const nbd_bcast_item* con
       if (items[0][k].bytes) live[r].push_back(items[r][k]);
     rows[r] = live[r].data();
   }
+  bool flat_seen = false;
   rc = run_tables(
-      c0, live[0].data(), (int)live[0].size(), g->world,
-      [&](int i0, int i1) { return launch_table<kMaxRanks>(c0, ctx, g->world, rows, i0, i1, (cudaStream_t)stream); },
+      c0, live[0].data(), (int)live[0].size(),
+      [&](int i0, int i1, bool flat) {
+        flat_seen = flat_seen || flat;
+        return launch_table<kMaxRanks>(c0, ctx, g->world, rows, i0, i1, flat, (cudaStream_t)stream);
+      },
       [&](int k) {
         void* bufs[kMaxRanks];
         for (int r = 0; r < g->world; ++r) bufs[r] = live[r][(size_t)k].buf;
         return nbd_emu_broadcast(any, bufs, live[0][(size_t)k].bytes, NBD_BYTES, live[0][(size_t)k].root, stream);
       });
-  set_algo(c0, "bcast_table");
+  set_algo(c0, flat_seen ? "bcast_flat" : "bcast_table");
   return rc;
 }
 

@@ -402,7 +402,7 @@ def body(rank: int, world: int, port: int) -> None:
         dist.broadcast(q, src=0)  # gloo
     for p, q in zip(params, ref):
         assert torch.equal(p.cpu(), q), "coalesced broadcast differs from gloo"
-    assert launches <= 2, f"7 small + 1 large broadcast took {launches} launches"
+    assert launches == 1, f"7 small + 1 large broadcast from one root took {launches} launches"
     # ---- sub-groups: dist.new_group over a subset gets its own communicator ----------------------
     if world >= 4:
         evens = dist.new_group(ranks=list(range(0, world, 2)), backend="cpu:gloo,cuda:b200")

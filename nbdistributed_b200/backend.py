@@ -86,6 +86,18 @@ def all_reduce_host(tensor, out=None, op: int = 0, group=None):
     return tensor if out is None else out
 
 
+def broadcast_tensors(tensors, src: int = 0, group=None) -> None:
+    """``for t in tensors: dist.broadcast(t, src)`` (the reference's parameter-sync idiom,
+    ref:README.md:122-123) as one call: tensors of any sizes and dtypes travel as one pipelined
+    launch per 256 tensors.  ``src`` is the global rank, as in ``dist.broadcast``.  Stream-ordered
+    on the current CUDA stream; the same result as the loop, bit for bit."""
+    import torch.distributed as dist
+
+    be = get_backend(group)
+    root = dist.get_group_rank(group, src) if group is not None else int(src)
+    be.broadcast_many(list(tensors), root)
+
+
 def launch_count() -> int:
     """Kernels launched by the native library in this process (bench.py's gpu_launches)."""
     return int(_load_ext().launch_count())

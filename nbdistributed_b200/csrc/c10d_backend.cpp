@@ -736,6 +736,31 @@ class BackendB200 : public c10d::Backend {
     has_last_ = true;
   }
 
+  // A list of tensors from one root in one call (a state_dict, a module's parameters): what the
+  // per-parameter broadcast loop of ref:README.md:122-123 does, without one dispatcher trip per
+  // tensor.  Stream-ordered on the current stream, like the loop it replaces.
+  void broadcast_many(std::vector<at::Tensor> tensors, int64_t root) {
+    TORCH_CHECK(root >= 0 && root < getSize(), "[b200] invalid root rank ", root);
+    if (tensors.empty()) return;
+    std::vector<nbd_bcast_item> items;
+    items.reserve(tensors.size());
+    const c10::DeviceIndex dev = tensors[0].get_device();
+    for (auto& t : tensors) {
+      check_tensor(t);
+      TORCH_CHECK(t.get_device() == dev, "[b200] broadcast_many: tensors on different devices");
+      items.push_back(nbd_bcast_item{t.data_ptr(), (size_t)t.nbytes(), (int)root});
+    }
+    std::lock_guard<std::mutex> lk(mu_);
+    ensure_comm(dev);
+    c10::cuda::CUDAGuard g(dev);
+    auto stream = c10::cuda::getCurrentCUDAStream(dev);
+    if (has_last_ && *last_stream_ != stream) last_done_.block(stream);
+    NBD_CHECK(nbd_broadcast_table(comm_, items.data(), (int)items.size(), stream.stream()), "broadcast_many");
+    last_done_.record(stream);
+    last_stream_ = stream;
+    has_last_ = true;
+  }
+
   // all_reduce of CPU tensors through the GPUs: nbd_all_reduce_host pipelines H2D, the
   // collective and D2H in chunks.  Returns when `recv` holds the result (CPU-tensor semantics).
   void all_reduce_host(at::Tensor send, at::Tensor recv, int64_t op) {
@@ -946,6 +971,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
            py::call_guard<py::gil_scoped_release>())
       .def("repeat_all_reduce", &BackendB200::repeat_all_reduce, py::call_guard<py::gil_scoped_release>())
       .def("repeat_broadcast", &BackendB200::repeat_broadcast, py::call_guard<py::gil_scoped_release>())
+      .def("broadcast_many", &BackendB200::broadcast_many, py::arg("tensors"), py::arg("root"),
+           py::call_guard<py::gil_scoped_release>())
       .def("device_index", &BackendB200::device_index)
       .def("set_inline_sync_ops", &BackendB200::set_inline_sync_ops);
   m.def("create_backend", &create_backend, py::arg("store"), py::arg("rank"), py::arg("size"), py::arg("timeout"),

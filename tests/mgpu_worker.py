@@ -403,6 +403,18 @@ def body(rank: int, world: int, port: int) -> None:
     for p, q in zip(params, ref):
         assert torch.equal(p.cpu(), q), "coalesced broadcast differs from gloo"
     assert launches == 1, f"7 small + 1 large broadcast from one root took {launches} launches"
+    # the same list as one call, from the last rank, mixed dtypes
+    torch.manual_seed(100 + rank)
+    mixed = [torch.randn(n, device=dev).to(dt) for n, dt in ((5, torch.float64), (70001, torch.bfloat16), (3 << 20, torch.float32), (1, torch.float16))]
+    mixed.append(torch.randint(0, 255, (12345,), device=dev, dtype=torch.uint8))
+    ref = [p.cpu().clone() for p in mixed]
+    B.broadcast_tensors(mixed, src=world - 1)
+    torch.cuda.synchronize()
+    assert B.get_backend().last_algo() == "bcast_flat", B.get_backend().last_algo()
+    for q in ref:
+        dist.broadcast(q, src=world - 1)  # gloo
+    for p, q in zip(mixed, ref):
+        assert torch.equal(p.cpu().view(torch.uint8), q.view(torch.uint8)), "broadcast_tensors differs from gloo"
     # ---- sub-groups: dist.new_group over a subset gets its own communicator ----------------------
     if world >= 4:
         evens = dist.new_group(ranks=list(range(0, world, 2)), backend="cpu:gloo,cuda:b200")

@@ -92,7 +92,8 @@ def main():
     ms3 = timed(bcast_all, 5, 1)
     small = [t for t in tensors if t.numel() * 4 <= 12 * 1024]
     ms_small = timed(lambda: [dist.broadcast(t, src=0) for t in small], 5, 1)
-    # the same loop inside a c10d coalescing block: the 98 small tensors become one table launch
+    # the same loop inside a c10d coalescing block: all 149 tensors share root 0 and become ONE
+    # flat-table launch (csrc/nbd_table.cuh, k_bcast_flat)
     def bcast_coalesced():
         with dist._coalescing_manager(device=dev):
             for t in tensors:
@@ -114,8 +115,41 @@ def main():
     if nccl is not None:
         ms3n = timed(lambda: [dist.broadcast(t, src=0, group=nccl) for t in tensors], 5, 1)
         line3["nccl_ms_total"] = round(ms3n, 3)
+    n0 = B.launch_count()
+    bcast_coalesced()
+    torch.cuda.synchronize()
+    line3["coalesced_launches"] = B.launch_count() - n0
+    line3["coalesced_algo"] = be.last_algo()
+    # the same list as ONE call (no per-tensor dispatcher trip on the host)
+    for t in tensors[1:]:
+        if rank != 0:
+            t.zero_()
+    B.broadcast_tensors(tensors, src=0)
+    torch.cuda.synchronize()
+    chk3 = torch.stack([t.view(torch.int32).sum(dtype=torch.int64) for t in tensors]).cpu()
+    line3["one_call_identical"] = bool(torch.equal(chk3, allc[0]))
+    ms3o = timed(lambda: B.broadcast_tensors(tensors, src=0), 5, 1)
+    line3["one_call_ms_total"] = round(ms3o, 3)
+    line3["one_call_effective_GBps"] = round(total / ms3o / 1e6, 1)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        bcast_coalesced()
+    host_us = (time.perf_counter() - t0) / 3 * 1e6
+    torch.cuda.synchronize()
+    line3["coalesced_host_issue_us"] = round(host_us, 1)
+    if "--only-cfg3" in sys.argv:  # pipeline-chunk sweep of the flat table
+        sweep = {}
+        for mib in (16, 32, 128, 256):
+            be.set_tunable("chunk_bytes", mib << 20)
+            sweep[f"{mib}MiB"] = round(timed(lambda: B.broadcast_tensors(tensors, src=0), 5, 1), 3)
+        be.set_tunable("chunk_bytes", 0)
+        line3["one_call_ms_by_chunk"] = sweep
     emit(line3)
     del tensors
+    if "--only-cfg3" in sys.argv:
+        dist.barrier(group=cpu)
+        W.shutdown_worker()
+        return
 
     # ---------------- cfg4: DDP-style bf16 gradient buckets, 1.236 G params ----------------
     params = 1_235_814_400

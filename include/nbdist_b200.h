@@ -223,13 +223,17 @@ int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends,
                            int op, void* stream);
 int nbd_emu_barrier(nbd_comm_t any, void* stream);
 
-/* ---- many small broadcasts at once -------------------------------------------------
+/* ---- many broadcasts at once ---------------------------------------------------------
  * The reference's broadcast idiom is one dist.broadcast per parameter (ref:README.md:122-123);
  * issued inside a c10d coalescing block (Backend::startCoalescing / endCoalescing,
- * $TORCH/.../Backend.hpp:109-123) the small ones arrive here as ONE call: every rank packs the
- * items it is root of into its peers' staging, one flag barrier, every rank unpacks the rest.
- * Every rank passes the same list of (bytes, root) in the same order; items may have different
- * roots; an item too large to share a table runs as an ordinary nbd_broadcast. */
+ * $TORCH/.../Backend.hpp:109-123) they arrive here as ONE call.  Every rank passes the same list
+ * of (bytes, root) in the same order.  The list is taken 256 items at a time:
+ *   - items that share a root and exceed 256 KiB together run as one flat table: the packed
+ *     list moves as one chunked scatter pipeline (any total size, one launch);
+ *   - otherwise (small, or mixed roots): every rank packs the items it is root of into its peers'
+ *     staging, one flag barrier, every rank unpacks the rest; an item too large to share such a
+ *     table runs as an ordinary nbd_broadcast.
+ * Result: bit-identical to nitems calls of nbd_broadcast in list order. */
 typedef struct {
   void* buf; /* device pointer: read on the root, written elsewhere */
   size_t bytes;

@@ -135,7 +135,9 @@ struct nbd_comm {
   uint64_t t_nvls_reduce = 0;   // 1: float SUM/AVG all_reduce may use in-switch reduction (order != rank order)
   uint64_t t_nvls_off = 0;      // 1: never use the multicast kernels
   uint64_t t_nvls_min = 0;      // smallest message for the multicast kernels
-  uint64_t t_pipe = 0;          // 1: force the tile-pipeline kernels (P2P transport) where they apply; 2: never
+  uint64_t t_pipe = 0;          // 1: force the tile-pipeline kernels (P2P transport) where they apply; 2: never;
+                                // 3: force the relay broadcast (all_reduce as with 0)
+  uint64_t t_relay_min = 0;     // broadcasts from this size on use the relay kernel (0 = default)
   uint64_t t_pipe_tile = 0;     // tile bytes per CTA per round (0 = planner's choice)
   uint64_t t_pipe_depth = 0;    // staging slots per CTA (0 = default)
   uint64_t t_pipe_mode = 0;     // bit 1: two reducing groups; bit 2: 8 loads in flight per thread (0 = default)

@@ -42,6 +42,10 @@ const void* pipe_broadcast_kernel(bool emu, bool mc) {
   return emu ? (const void*)k_broadcast_pipe<kMaxRanks, false> : (const void*)k_broadcast_pipe<1, false>;
 }
 
+const void* relay_broadcast_kernel(bool emu) {
+  return emu ? (const void*)k_broadcast_relay<kMaxRanks> : (const void*)k_broadcast_relay<1>;
+}
+
 size_t pipe_smem_bytes() { return kPipeSmemBytes; }
 
 const void* mcz_allreduce_kernel(int dtype) {

@@ -20,6 +20,7 @@ const void* zc_reduce_kernel(int zkind, int dtype, bool sum, bool emu);
 // switch cannot do the reduction); all need pipe_smem_bytes() of dynamic shared memory
 const void* pipe_allreduce_kernel(int dtype, bool sum, bool emu, bool mc);
 const void* pipe_broadcast_kernel(bool emu, bool mc);
+const void* relay_broadcast_kernel(bool emu);  // k_broadcast_relay: scatter + relay, peer-to-peer transport
 size_t pipe_smem_bytes();
 // zero-copy in-switch all_reduce on multicast-pool memory (f32/bf16/f16 sums); args: Pack<1>, McPtrs, OpParams
 const void* mcz_allreduce_kernel(int dtype);

@@ -360,6 +360,7 @@ static uint64_t* tunable_slot(nbd_comm* c, const char* name) {
   if (!strcmp(name, "debug_mute_rank")) return &c->t_debug_mute;
   if (!strcmp(name, "pipe_depth")) return &c->t_pipe_depth;
   if (!strcmp(name, "pipe_mode")) return &c->t_pipe_mode;
+  if (!strcmp(name, "relay_min_bytes")) return &c->t_relay_min;
   if (!strcmp(name, "nvls_bcast")) return &c->t_nvls_bcast;
   return nullptr;
 }
@@ -725,6 +726,15 @@ static bool nvls_bcast_wanted(const nbd_comm* c, u64 bytes) {
 // P2P tile pipeline: only on request ("pipe" = 1) until measurements say where it wins
 static bool pipe_wanted(const nbd_comm* c, u64 bytes) { return c->t_pipe == 1 && bytes > kLLMaxBytes; }
 
+// Relay broadcast (k_broadcast_relay: the scatter algorithm with per-tile flags).  "pipe" = 3
+// forces it; otherwise from "relay_min_bytes" on (0 = the default below).
+static const u64 kDefRelayMin = ~0ull;
+static bool relay_wanted(const nbd_comm* c, u64 bytes) {
+  if (c->t_pipe == 3) return bytes > kLLMaxBytes;
+  if (c->t_pipe != 0 || c->world <= 2) return false;
+  return bytes >= (c->t_relay_min ? c->t_relay_min : kDefRelayMin);
+}
+
 static void fill_pipe(PackPipe<1>& pk, nbd_comm* c, const void* send, void* recv, bool mc) {
   memset(&pk, 0, sizeof(pk));
   pk.ctx[0] = c->ctx;
@@ -751,16 +761,20 @@ static int pipe_all_reduce(nbd_comm* c, const void* send, void* recv, u64 bytes,
   return pipe_launch(fn, c->device, p.nblocks, 1, false, s, &pk, &p.op);
 }
 
-static int pipe_broadcast(nbd_comm* c, void* buf, u64 bytes, int root, bool mc, cudaStream_t s) {
-  const void* fn = pipe_broadcast_kernel(false, mc);
+// two pushing groups unless "pipe_mode" says otherwise (any non-zero value without bit 1: one group)
+static int relay_mode(const nbd_comm* c) { return c->t_pipe_mode ? (int)(c->t_pipe_mode & 2) : 2; }
+
+static int pipe_broadcast(nbd_comm* c, void* buf, u64 bytes, int root, bool mc, cudaStream_t s, bool relay = false) {
+  const void* fn = relay ? relay_broadcast_kernel(false) : pipe_broadcast_kernel(false, mc);
   Plan p;
   int rc = plan_pipe(c, bytes, mc ? (u64)c->nvls.stage_bytes : 2 * c->ctx.half_bytes, 0, &p);
   if (rc != NBD_OK) return rc;
   p.op.root = root;
   p.op.algo |= mc ? 0 : 1;
+  if (relay) p.op.algo = 1 | relay_mode(c);
   PackPipe<1> pk;
   fill_pipe(pk, c, buf, buf, mc);
-  c->last_algo = mc ? "bcast_nvls" : "bcast_pipe";
+  c->last_algo = relay ? "bcast_relay" : (mc ? "bcast_nvls" : "bcast_pipe");
   return pipe_launch(fn, c->device, p.nblocks, 1, false, s, &pk, &p.op);
 }
 
@@ -1313,6 +1327,7 @@ int nbd_broadcast(nbd_comm_t c, void* buf, size_t count, int dtype, int root, vo
   cudaStream_t s = (cudaStream_t)stream;
   if (nvls_bcast_wanted(c, (u64)count * es)) return pipe_broadcast(c, buf, (u64)count * es, root, true, s);
   if (pipe_wanted(c, (u64)count * es)) return pipe_broadcast(c, buf, (u64)count * es, root, false, s);
+  if (relay_wanted(c, (u64)count * es)) return pipe_broadcast(c, buf, (u64)count * es, root, false, s, true);
   Plan p = plan_broadcast(c, (u64)count * es, root, 0);
   Pack<1> pk;
   fill_pack(pk, c, buf, buf);
@@ -1475,11 +1490,13 @@ int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count, int dtype
   if (g->world == 1) return NBD_OK;
   nbd_comm* c0 = g->comms[0];
   DeviceGuard dg(c0->device);
-  if (pipe_wanted(c0, (u64)count * es)) {
+  const bool relay = relay_wanted(c0, (u64)count * es);
+  if (relay || pipe_wanted(c0, (u64)count * es)) {
     Plan p;
     if ((rc = plan_pipe(c0, (u64)count * es, 2 * c0->ctx.half_bytes, g->world, &p)) != NBD_OK) return rc;
     p.op.root = root;
     p.op.algo |= 1;
+    if (relay) p.op.algo = 1 | relay_mode(c0);
     PackPipe<kMaxRanks> pk;
     memset(&pk, 0, sizeof(pk));
     for (int r = 0; r < g->world; ++r) {
@@ -1490,8 +1507,8 @@ int nbd_emu_broadcast(nbd_comm_t any, void* const* bufs, size_t count, int dtype
       pk.pb[r].local = g->comms[r]->ctx.stage[r];
     }
     mute_rank(g, pk.ctx);
-    set_algo(c0, "bcast_pipe");
-    return pipe_launch(pipe_broadcast_kernel(true, false), c0->device, p.nblocks, g->world, true, (cudaStream_t)stream, &pk,
+    set_algo(c0, relay ? "bcast_relay" : "bcast_pipe");
+    return pipe_launch(relay ? relay_broadcast_kernel(true) : pipe_broadcast_kernel(true, false), c0->device, p.nblocks, g->world, true, (cudaStream_t)stream, &pk,
                        &p.op);
   }
   Pack<kMaxRanks> pk;

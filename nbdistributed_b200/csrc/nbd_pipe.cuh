@@ -515,6 +515,164 @@ k_broadcast_pipe(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
   pipe_close(c, E, g.rounds, op);
 }
 
+// ---------------------------------------------------------------------------
+// broadcast as a relay through the tile pipeline (peer-to-peer transport, any world size).
+// k_broadcast's "scatter" algorithm with per-tile flags instead of whole-grid barriers: tile i of
+// CTA b is cut into N-1 sub-shards, one per non-root rank.
+//   root      PUSH warps (2..15) read the tile from its user buffer and write sub-shard j into
+//             ITS OWNER's slot only (root egress = S), then signal A(i) to every other rank
+//   non-root  PUSH warps wait A(i), read the own sub-shard from the local slot and write it into
+//             the slots of the other N-2 non-root ranks, signal B(i) to them
+//             OUT warp (1) waits A(i) and the N-2 B(i), copies the whole tile slot -> user (TMA
+//             ring), then signals D(i) = "my slot of tile i is free" to every other rank
+// A writer (root or relaying peer) reuses a slot for tile i+depth after D(i) of its owner.
+// Every transfer is a store and every wait polls local memory.  Flag words: A and D share flag
+// row b (word = source rank: the root's word carries A, a non-root's word D), B lives in row
+// kPipeRowB + b; all carry E+1+i, below the closing barrier's E+rounds+1.
+// op.algo bit 1: the 14 PUSH warps work as two groups on alternate tiles (the release before a
+// signal drains the group's remote stores; the other group keeps the links busy meanwhile).
+// ---------------------------------------------------------------------------
+template <int NCTX>
+__global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
+k_broadcast_relay(const __grid_constant__ PackPipe<NCTX> pk, const OpParams op) {
+  extern __shared__ __align__(128) unsigned char pipe_smem[];
+  __shared__ uint64_t bars[kTmaStages];
+  __shared__ volatile u32 sig_next;  // tiles [0, sig_next) have been pushed and signalled, in order
+
+  const int ci = ctx_index<NCTX>();
+  const RankCtx& c = pk.ctx[ci];
+  const RankBufs& ub = pk.buf[ci];
+  const PipeBufs& pb = pk.pb[ci];
+  const int N = c.world, r = c.rank, root = op.root;
+  KernelClock clk = kernel_begin(c);
+  PipeGeom g;
+  g.units = units_of(op.bytes);
+  g.tu = op.chunk_bytes / kUnit;
+  g.rounds = op.nchunks;
+  g.depth = (u32)op.depth;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const u64 rowA = (u64)blockIdx.x * kMaxRanks, rowB = (u64)(kPipeRowB + blockIdx.x) * kMaxRanks;
+  const int nsh = N - 1;
+  auto owner_of = [&](int j) { int p = root + 1 + j; if (p >= N) p -= N; return p; };
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kTmaStages; ++s) mbar_init(&bars[s], 1);
+    sig_next = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  const u64 E = pipe_open(c, clk, op);
+
+  if (warp >= 2) {
+    const int ngroups = (op.algo & 2) ? 2 : 1;
+    const int nthr = kPipeRedThreads / ngroups;
+    const int rt = threadIdx.x - 64;
+    const int grp = rt / nthr, gt = rt - grp * nthr;
+    const bool peer_lane = gt < N && gt != r && gt != root;  // lanes that talk to the other non-root ranks
+    const Region src = make_region(ub.recv, op.bytes);
+    const bool al = region_aligned(src);
+    for (u32 i = (u32)grp; i < g.rounds; i += (u32)ngroups) {
+      const u64 tu = tile_units(g, i), first = tile_first(g, i), soff = slot_offset(g, i);
+      const u64 su = (tu + nsh - 1) / nsh;
+      if (r == root) {
+        // slot free on every owner: D(i - depth)
+        if (i >= g.depth && gt < N && gt != r) wait_flag(c, c.flags[r] + rowA + gt, E + 1 + (i - g.depth));
+        named_bar_sync(1 + grp, nthr);
+        for (int jj = 0; jj < nsh; ++jj) {
+          int j = jj + (int)((blockIdx.x + i) % (u32)nsh);  // CTAs start on different owners
+          if (j >= nsh) j -= nsh;
+          u64 lo = (u64)j * su;
+          if (lo > tu) lo = tu;
+          u64 hi = lo + su;
+          if (hi > tu) hi = tu;
+          char* dst = c.stage[owner_of(j)] + soff;
+          for (u64 b0 = lo + gt; b0 < hi; b0 += 4ull * nthr) {
+            uint4 v[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const u64 u = b0 + (u64)q * nthr;
+              if (u < hi) v[q] = region_ld(src, al, first + u);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const u64 u = b0 + (u64)q * nthr;
+              if (u < hi) st16(dst + u * kUnit, v[q]);
+            }
+          }
+        }
+      } else {
+        if (gt == 0) wait_flag(c, c.flags[r] + rowA + root, E + 1 + i);                             // own sub-shard is here
+        if (i >= g.depth && peer_lane) wait_flag(c, c.flags[r] + rowA + gt, E + 1 + (i - g.depth));  // peers' slots are free
+        named_bar_sync(1 + grp, nthr);
+        int j = r - root - 1;
+        if (j < 0) j += N;
+        u64 lo = (u64)j * su;
+        if (lo > tu) lo = tu;
+        u64 hi = lo + su;
+        if (hi > tu) hi = tu;
+        const char* from = pb.local + soff;
+        for (u64 b0 = lo + gt; b0 < hi; b0 += 4ull * nthr) {
+          uint4 v[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const u64 u = b0 + (u64)q * nthr;
+            if (u < hi) v[q] = ld16(from + u * kUnit);
+          }
+#pragma unroll
+          for (int k = 1; k < kMaxRanks; ++k) {
+            if (k < N) {
+              int p = r + k;
+              if (p >= N) p -= N;
+              if (p != root) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const u64 u = b0 + (u64)q * nthr;
+                  if (u < hi) st16(c.stage[p] + soff + u * kUnit, v[q]);
+                }
+              }
+            }
+          }
+        }
+      }
+      named_bar_sync(1 + grp, nthr);
+      if (gt < N) {
+        // flags only grow and a signal for tile i must imply the one for i-1: groups signal in tile order
+        while (sig_next != i) {
+        }
+        if (r == root) {
+          if (gt != r) st_release_sys(c.flags[gt] + rowA + r, E + 1 + i);  // A(i)
+        } else if (peer_lane) {
+          st_release_sys(c.flags[gt] + rowB + r, E + 1 + i);  // B(i)
+        }
+        __syncwarp((1u << N) - 1u);
+        if (gt == 0) {
+          __threadfence_block();
+          sig_next = i + 1;
+        }
+      }
+    }
+  } else if (warp == 1 && r != root) {
+    TmaRing R = {pipe_smem, bars, 0};
+    const Region dst = make_region(ub.recv, op.bytes);
+    for (u32 i = 0; i < g.rounds; ++i) {
+      if (lane == root) wait_flag(c, c.flags[r] + rowA + root, E + 1 + i);
+      else if (lane < N && lane != r) wait_flag(c, c.flags[r] + rowB + lane, E + 1 + i);
+      __syncwarp();
+      if (lane == 0) fence_proxy_async();  // acquired data is read by the async proxy next
+      __syncwarp();
+      const u64 tu = tile_units(g, i);
+      if (tu) warp_tile_copy(R, dst, tile_first(g, i), tu, pb.local + slot_offset(g, i), false, lane);
+      if (lane == 0) {
+        bulk_wait_all0();  // slot fully read, user memory written
+        while (sig_next < i + 1) {  // ... and this rank's PUSH warps are done reading it too
+        }
+      }
+      __syncwarp();
+      if (lane < N && lane != r) st_release_sys(c.flags[lane] + rowA + r, E + 1 + i);  // D(i)
+    }
+  }
+  pipe_close(c, E, g.rounds, op);
+}
+
 // all_reduce on symmetric memory from the multicast pool (nbd_mem_alloc): no staging at all.
 // Barrier, rank r sums shard r inside the switch and writes it to every rank, barrier.
 // send_mc / recv_mc are multicast aliases; op.bytes is a multiple of 16 (the host checks).

@@ -222,3 +222,136 @@ def test_pipe_256mib_properties(torch_cuda):
         wf = want.to(torch.float32)
         for r in range(world):
             assert torch.equal(t[r], wf), f"rank {r}"
+
+
+# ---- relay broadcast (k_broadcast_relay): scatter + relay with per-tile flags --------------------
+
+@pytest.fixture(scope="module")
+def relay_groups(torch_cuda):
+    from nbdistributed_b200 import capi
+
+    made = {}
+
+    def get(world):
+        if world not in made:
+            made[world] = capi.EmuGroup(world, device=0, stage_bytes=16 << 20)
+            made[world].set_tunable("pipe", 3)
+        return made[world]
+
+    yield get
+    for g in made.values():
+        g.close()
+
+
+def _relay_bcast(torch, grp, world, nbytes, root, seed, offset=0):
+    x = O.make_inputs(world, nbytes, "u8", seed=seed)
+    backing = [torch.zeros(nbytes + 64, dtype=torch.uint8, device="cuda:0") for _ in range(world)]
+    views = [b[offset:offset + nbytes] for b in backing]
+    for v, a in zip(views, x):
+        v.copy_(H.to_cuda(a, "u8"))
+    grp.broadcast(views, root=root)
+    assert grp.last_algo() == "bcast_relay", grp.last_algo()
+    return x, backing, views
+
+
+def _relay_check(torch, world, nbytes, root, x, backing, views, offset, what):
+    for r in range(world):
+        H.assert_same(H.to_numpy(views[r], "u8"), x[root], "u8", f"{what}: root {root} rank {r}")
+        assert int(backing[r][:offset].sum()) == 0 and int(backing[r][offset + nbytes:].sum()) == 0, f"{what}: rank {r} wrote outside the view"
+
+
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
+@pytest.mark.parametrize("nbytes", [(32 << 10) + 16, 100_001, (1 << 20) + 17, (5 << 20) + 3])
+def test_relay_broadcast_every_root(torch_cuda, relay_groups, world, nbytes):
+    grp = relay_groups(world)
+    for root in range(world):
+        x, backing, views = _relay_bcast(torch_cuda, grp, world, nbytes, root, 31 + root)
+        torch_cuda.cuda.synchronize()
+        grp.async_error()
+        _relay_check(torch_cuda, world, nbytes, root, x, backing, views, 0, "aligned")
+
+
+@pytest.mark.parametrize("world", [3, 8])
+@pytest.mark.parametrize("offset", [1, 4, 8])
+def test_relay_broadcast_misaligned_views(torch_cuda, relay_groups, world, offset):
+    grp = relay_groups(world)
+    nbytes = (1 << 18) + 5
+    x, backing, views = _relay_bcast(torch_cuda, grp, world, nbytes, world - 1, 5, offset)
+    torch_cuda.cuda.synchronize()
+    grp.async_error()
+    _relay_check(torch_cuda, world, nbytes, world - 1, x, backing, views, offset, f"offset {offset}")
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("depth", [2, 4])
+@pytest.mark.parametrize("mode", [2, 4])
+@pytest.mark.parametrize("tile", [128, 8192])
+def test_relay_broadcast_shapes(torch_cuda, relay_groups, world, depth, mode, tile):
+    """Many short rounds: every slot reused tens of times; one or two pushing groups (mode 2 /
+    mode 4 = one group); sub-shards of a few units, some of them empty in the last tile."""
+    grp = relay_groups(world)
+    knobs = {"pipe_depth": depth, "pipe_mode": mode, "pipe_tile_bytes": tile, "blocks": 3}
+    for k, v in knobs.items():
+        grp.set_tunable(k, v)
+    try:
+        nbytes = 40_013 if tile < 4096 else (1 << 20) + 77
+        for root in (0, world - 1):
+            x, backing, views = _relay_bcast(torch_cuda, grp, world, nbytes, root, 70 + root)
+            torch_cuda.cuda.synchronize()
+            grp.async_error()
+            _relay_check(torch_cuda, world, nbytes, root, x, backing, views, 0, f"depth {depth} mode {mode} tile {tile}")
+    finally:
+        for k in knobs:
+            grp.set_tunable(k, 0)
+
+
+def test_relay_broadcast_interleaves_with_other_kernels(torch_cuda, relay_groups):
+    """Back-to-back relay broadcasts, chunked all_reduces and LL-size broadcasts on one stream,
+    roots rotating, no host sync in between."""
+    torch = torch_cuda
+    world = 4
+    grp = relay_groups(world)
+    rng = np.random.default_rng(9)
+    done = []
+    for it in range(30):
+        if it % 3 == 2:
+            dtype, numel = "f32", int(rng.integers(40_000, 600_000))
+            x = O.make_inputs(world, numel, dtype, seed=300 + it)
+            t = [H.to_cuda(a, dtype) for a in x]
+            grp.all_reduce(t, t)
+            done.append(("ar", dtype, x, None, t))
+        else:
+            nbytes = int(rng.integers(1_000, 3_000_000))
+            x = O.make_inputs(world, nbytes, "u8", seed=300 + it)
+            t = [H.to_cuda(a, "u8") for a in x]
+            grp.broadcast(t, root=it % world)
+            done.append(("bc", "u8", x, it % world, t))
+    torch.cuda.synchronize()
+    grp.async_error()
+    for kind, dtype, x, root, t in done:
+        want = O.reduce_rank_order(x, dtype) if kind == "ar" else x[root]
+        for r in range(world):
+            H.assert_same(H.to_numpy(t[r], dtype), want, dtype, f"{kind} rank {r}")
+
+
+def test_relay_broadcast_256mib(torch_cuda):
+    """BASELINE-size message (256 MiB, 4 ranks, default tile and depth): every rank ends with the
+    root's bytes."""
+    from nbdistributed_b200 import capi
+
+    torch = torch_cuda
+    world, nbytes = 4, 256 << 20
+    with capi.EmuGroup(world, device=0, stage_bytes=128 << 20) as grp:
+        grp.set_tunable("pipe", 3)
+        g = torch.Generator(device="cuda:0")
+        t = []
+        for r in range(world):
+            g.manual_seed(11 + r)
+            t.append(torch.randint(0, 256, (nbytes,), generator=g, device="cuda:0", dtype=torch.uint8))
+        want = t[2].clone()
+        grp.broadcast(t, root=2)
+        assert grp.last_algo() == "bcast_relay"
+        torch.cuda.synchronize()
+        grp.async_error()
+        for r in range(world):
+            assert torch.equal(t[r], want), f"rank {r}"

@@ -321,8 +321,10 @@ uint64_t nbd_launch_count(void);
 int nbd_comm_last_zc_decision(nbd_comm_t comm);
 /* What the planner would choose for a collective, computed on the host without touching a GPU
  * (tests of the host logic).  kind: 0 all_reduce, 1 reduce_scatter, 2 all_gather (bytes = one
- * rank's shard for 1 and 2), 3 broadcast.  out[6] = {algorithm, chunk_bytes, nchunks, CTAs,
- * bytes per staging half, offset of the LL area}.  stage_bytes 0 = default. */
+ * rank's shard for 1 and 2), 3 broadcast, 4 flat broadcast table (bytes = packed size of the
+ * table), 5 tile pipeline (chunk_bytes = tile bytes, nchunks = rounds per CTA, algorithm = slots
+ * per CTA).  out[6] = {algorithm, chunk_bytes, nchunks, CTAs, bytes per staging half, offset of
+ * the LL area}.  stage_bytes 0 = default. */
 int nbd_plan_query(int world_size, size_t stage_bytes, int num_sms, int emulated, int kind, size_t bytes,
                    uint64_t* out);
 /* Name of the algorithm the last collective on `comm` used

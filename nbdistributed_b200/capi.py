@@ -145,7 +145,7 @@ def plan_query(world: int, kind: str, nbytes: int, stage_bytes: int = 0, num_sms
     """The planner's choice for a collective (GPU-free): algorithm code, chunking, grid."""
     lib = load()
     out = (C.c_uint64 * 6)()
-    code = {"all_reduce": 0, "reduce_scatter": 1, "all_gather": 2, "broadcast": 3}[kind]
+    code = {"all_reduce": 0, "reduce_scatter": 1, "all_gather": 2, "broadcast": 3, "flat_table": 4, "pipe": 5}[kind]
     check(lib.nbd_plan_query(world, stage_bytes, num_sms, int(emulated), code, nbytes, out))
     return {"algo": int(out[0]), "chunk_bytes": int(out[1]), "nchunks": int(out[2]), "nblocks": int(out[3]),
             "half_bytes": int(out[4]), "ll_off": int(out[5])}

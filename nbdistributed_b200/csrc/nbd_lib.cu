@@ -2269,7 +2269,9 @@ extern "C" int nbd_emu_all_reduce_host(nbd_comm_t any, const void* const* host_s
 // nbd_plan_query — which algorithm / chunking / grid the planner picks, without a GPU
 // ---------------------------------------------------------------------------
 // kind: 0 all_reduce, 1 reduce_scatter (bytes = one shard), 2 all_gather (bytes = one shard),
-// 3 broadcast.  out: {algo, chunk_bytes, nchunks, nblocks, half_bytes, ll_off}.
+// 3 broadcast, 4 flat broadcast table (bytes = packed size), 5 tile pipeline (all_reduce_pipe,
+// broadcast_pipe, broadcast_relay: chunk_bytes = tile, nchunks = rounds, algo = slots per CTA).
+// out: {algo, chunk_bytes, nchunks, nblocks, half_bytes, ll_off}.
 extern "C" int nbd_plan_query(int world, size_t stage_bytes, int num_sms, int emu, int kind, size_t bytes, uint64_t* out) {
   if (!out || world < 2 || world > kMaxRanks || num_sms < 1) return fail(NBD_ERR_INVALID_ARGUMENT, "bad plan query");
   static std::mutex mu;
@@ -2289,6 +2291,13 @@ extern "C" int nbd_plan_query(int world, size_t stage_bytes, int num_sms, int em
     case 1: p = plan_reduce_scatter(&c, bytes, NBD_SUM, ew); break;
     case 2: p = plan_all_gather(&c, bytes, ew); break;
     case 3: p = plan_broadcast(&c, bytes, 0, ew); break;
+    case 4: p = plan_flat(&c, bytes, 0, ew); break;
+    case 5: {
+      int rc = plan_pipe(&c, bytes, 2 * c.ctx.half_bytes, ew, &p);
+      if (rc != NBD_OK) return rc;
+      p.op.algo = p.op.depth;
+      break;
+    }
     default: return fail(NBD_ERR_INVALID_ARGUMENT, "unknown collective kind %d", kind);
   }
   out[0] = (uint64_t)p.op.algo;

@@ -68,3 +68,36 @@ def test_emulated_ranks_share_the_sms():
     one = capi.plan_query(8, "all_reduce", 256 << 20, emulated=False)["nblocks"]
     emu = capi.plan_query(8, "all_reduce", 256 << 20, emulated=True)["nblocks"]
     assert one == 148 and emu == 148 // 8
+
+
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
+@pytest.mark.parametrize("stage", [0, 8 << 20, 2 << 20])
+def test_flat_table_chunks(world, stage):
+    """k_bcast_flat: chunks are whole numbers of (N-1) units, one shard fits a staging half, the
+    chunks cover the packed table, equal-sized."""
+    nsh = world - 1
+    for nbytes in [16 * k for k in (1, 7, 1000, 16385, 1 << 20, (40759296 + 15), 1 << 26)] + [652148736 + 16 * 149]:
+        nbytes = units(nbytes) * UNIT  # packed tables are whole units
+        p = capi.plan_query(world, "flat_table", nbytes, stage_bytes=stage)
+        chunk, n, half = p["chunk_bytes"], p["nchunks"], p["half_bytes"]
+        assert chunk % (UNIT * nsh) == 0 and chunk > 0
+        assert n * chunk >= nbytes > (n - 1) * chunk
+        assert (units(chunk) // nsh) * UNIT <= half
+        assert 1 <= p["nblocks"] <= 148
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("stage", [0, 16 << 20])
+@pytest.mark.parametrize("emulated", [False, True])
+def test_tile_pipeline_geometry(world, stage, emulated):
+    """plan_pipe: grid x slots x tile fits both staging halves, tiles are 128-byte multiples,
+    grid x rounds x tile covers the message, the grid respects the flag rows of the B flags."""
+    for nbytes in [(32 << 10) + 16, 100_001, 1 << 20, (5 << 20) + 3, 64 << 20, 256 << 20, 1 << 30]:
+        p = capi.plan_query(world, "pipe", nbytes, stage_bytes=stage, emulated=emulated)
+        tile, rounds, grid, depth = p["chunk_bytes"], p["nchunks"], p["nblocks"], p["algo"]
+        assert tile % 128 == 0 and tile >= 128
+        assert 2 <= depth <= 8
+        assert grid * depth * tile <= 2 * p["half_bytes"]
+        assert grid * rounds * tile >= nbytes
+        assert grid * (rounds - 1) * tile < units(nbytes) * UNIT
+        assert 1 <= grid <= (148 // world if emulated else 148)

@@ -60,14 +60,19 @@ struct RankCtx {
   u64 half_bytes;   // bytes in one staging half (multiple of 16)
   u64 timeout_ns;   // 0 = never
   u64 ll_off;       // offset of the LL area inside every rank's staging (0: no LL area)
+  u64 ll_slot;      // bytes of one source rank's slot in the LL area (2 x the LL payload limit)
   u64 p2p_off;      // offset of the point-to-point area (nbd_p2p.cuh) from every rank's staging base (0: none)
 };
 
 // LL ("low latency") area at the tail of the staging region: for each parity, one slot per
-// source rank; a slot holds kLLMaxBytes of payload as 8-byte {data32, flag32} packets.
+// source rank; a slot (RankCtx::ll_slot bytes) holds the LL payload limit of the communicator as
+// 8-byte {data32, flag32} packets.  The limit is kLLBigMax when the staging is large enough to
+// spare 8 MiB for it, else kLLMaxBytes (small test arenas).
 constexpr u64 kLLMaxBytes = 32ull << 10;
-constexpr u64 kLLSlotBytes = 2 * kLLMaxBytes;
-constexpr u64 kLLAreaBytes = 2 * (u64)kMaxRanks * kLLSlotBytes;  // 1 MiB
+constexpr u64 kLLBigMax = 256ull << 10;
+constexpr u64 kLLBigStage = 64ull << 20;  // staging sizes from here on carry the large LL area
+__host__ __device__ constexpr u64 ll_cap_of(u64 stage_bytes) { return stage_bytes >= kLLBigStage ? kLLBigMax : kLLMaxBytes; }
+__host__ __device__ constexpr u64 ll_area_of(u64 stage_bytes) { return 2 * (u64)kMaxRanks * 2 * ll_cap_of(stage_bytes); }  // 1 or 8 MiB
 // Row of the flag array where rank `src` publishes "LL broadcasts I have finished reading" (word
 // = src, value = sequence number + 1).  A rank that WRITES packets for LL operation s must know
 // that every receiver has finished operation s-2, the previous user of the same parity buffer.

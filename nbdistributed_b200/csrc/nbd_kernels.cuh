@@ -198,7 +198,7 @@ k_allreduce_oneshot(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
 
 
 // ---------------------------------------------------------------------------
-// all_reduce, LL one-shot (latency path, <= kLLMaxBytes): every 4-byte word travels with its
+// all_reduce, LL one-shot (latency path, up to the communicator's LL limit): every 4-byte word travels with its
 // own 4-byte flag in one 8-byte packet, so the receiver needs no separate flag, no fence and
 // no barrier: it spins on the packets themselves.  A unit of 16 payload bytes is two 16-byte
 // stores {w0,f,w1,f} {w2,f,w3,f}; each 8-byte half is written atomically.  flag = operation
@@ -260,7 +260,7 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   const volatile LocalState* st = c.state;
   const u64 seq = st->ll_seq, hist = st->ll_hist;
   const u32 flag = (u32)(seq % 0xfffffffeull) + 1u;
-  const u64 par = (seq & 1) * (u64)kMaxRanks * kLLSlotBytes;
+  const u64 par = (seq & 1) * (u64)kMaxRanks * c.ll_slot;
   const Region src = make_region(ub.send, op.bytes), dst = make_region(ub.recv, op.bytes);
   const bool als = region_aligned(src), ald = region_aligned(dst);
   const u64 units = units_of(op.bytes);
@@ -268,26 +268,36 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   block_span(units, units, lo, hi);
   char* my_ll = c.stage[r] + c.ll_off + par;
   ll_wait_acks(c, seq, hist);
+  // Phase 1: every packet of this CTA's span goes out before anything is awaited, so a span of
+  // several units per thread costs one flight time, not one per unit.
+  const bool single = hi - lo <= (u64)kThreads;  // one unit per thread: keep it in registers
+  uint4 first = make_uint4(0, 0, 0, 0);
   for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
-    uint4 v[kMaxRanks];
     const uint4 mine = region_ld(src, als, i);
+    if (single) first = mine;
 #pragma unroll
     for (int k = 1; k < kMaxRanks; ++k) {
       if (k < N) {
         int p = r + k;
         if (p >= N) p -= N;
-        char* d = c.stage[p] + c.ll_off + par + (u64)r * kLLSlotBytes + i * 32;
+        char* d = c.stage[p] + c.ll_off + par + (u64)r * c.ll_slot + i * 32;
         st_ll(d, mine.x, mine.y, flag);
         st_ll(d + 16, mine.z, mine.w, flag);
       }
     }
+  }
+  // Phase 2: spin on the peers' packets, reduce in ascending rank order.  (In place: unit i of the
+  // send buffer is read again here before unit i of the result is written, by the same thread.)
+  for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
+    uint4 v[kMaxRanks];
+    const uint4 mine = single ? first : region_ld(src, als, i);
 #pragma unroll
     for (int k = 0; k < kMaxRanks; ++k) {
       if (k < N) {
         if (k == r) {
           v[k] = mine;
         } else {
-          const char* s = my_ll + (u64)k * kLLSlotBytes + i * 32;
+          const char* s = my_ll + (u64)k * c.ll_slot + i * 32;
           uint4 a = ld_ll(s), b = ld_ll(s + 16);
           u32 spins = 0;
           u64 t0 = 0;
@@ -318,7 +328,7 @@ k_allreduce_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   ll_finish(c, seq, hist, false);
 }
 
-// broadcast, LL (<= kLLMaxBytes): the root writes {data, flag} packets into its slot of every
+// broadcast, LL (up to the communicator's LL limit): the root writes {data, flag} packets into its slot of every
 // peer's LL area, the peers spin on the packets and copy them out.  No barrier, no fence.
 template <int NCTX>
 __global__ void __launch_bounds__(kThreads, kMinBlocksPerSM)
@@ -330,7 +340,7 @@ k_broadcast_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   const volatile LocalState* st = c.state;
   const u64 seq = st->ll_seq, hist = st->ll_hist;
   const u32 flag = (u32)(seq % 0xfffffffeull) + 1u;
-  const u64 par = (seq & 1) * (u64)kMaxRanks * kLLSlotBytes;
+  const u64 par = (seq & 1) * (u64)kMaxRanks * c.ll_slot;
   const Region buf = make_region(ub.recv, op.bytes);
   const bool al = region_aligned(buf);
   const u64 units = units_of(op.bytes);
@@ -345,14 +355,14 @@ k_broadcast_ll(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
         if (k < N) {
           int p = r + k;
           if (p >= N) p -= N;
-          char* d = c.stage[p] + c.ll_off + par + (u64)r * kLLSlotBytes + i * 32;
+          char* d = c.stage[p] + c.ll_off + par + (u64)r * c.ll_slot + i * 32;
           st_ll(d, mine.x, mine.y, flag);
           st_ll(d + 16, mine.z, mine.w, flag);
         }
       }
     }
   } else {
-    const char* slot = c.stage[r] + c.ll_off + par + (u64)root * kLLSlotBytes;
+    const char* slot = c.stage[r] + c.ll_off + par + (u64)root * c.ll_slot;
     for (u64 i = lo + threadIdx.x; i < hi; i += kThreads) {
       const char* s = slot + i * 32;
       uint4 a = ld_ll(s), b = ld_ll(s + 16);

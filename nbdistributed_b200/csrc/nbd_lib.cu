@@ -78,7 +78,7 @@ static int alloc_rank(nbd_comm* c, size_t stage_bytes) {
   c->num_sms = prop.multiProcessorCount;
   NBD_CUDA(cudaMalloc((void**)&c->arena, c->arena_bytes));
   NBD_CUDA(cudaMemset(c->arena, 0, kFlagBytes));
-  NBD_CUDA(cudaMemset(c->arena + kFlagBytes + stage_bytes - kLLAreaBytes, 0, kLLAreaBytes));  // LL flags start at 0
+  NBD_CUDA(cudaMemset(c->arena + kFlagBytes + stage_bytes - ll_area_of(stage_bytes), 0, ll_area_of(stage_bytes)));  // LL flags start at 0
   NBD_CUDA(cudaMalloc((void**)&c->state, sizeof(LocalBlock)));  // LocalState is its first member
   NBD_CUDA(cudaMemset(c->state, 0, sizeof(LocalBlock)));
   if (!c->emu) {
@@ -122,10 +122,11 @@ static void fill_ctx(nbd_comm* c) {
   }
   x.state = c->state;
   x.mbox = c->mbox_dev;
-  // the last MiB of staging is the LL area; the two pipeline halves share the rest
-  x.ll_off = c->stage_bytes - kLLAreaBytes;
+  // the tail of the staging (1 or 8 MiB) is the LL area; the two pipeline halves share the rest
+  x.ll_off = c->stage_bytes - ll_area_of(c->stage_bytes);
+  x.ll_slot = 2 * ll_cap_of(c->stage_bytes);
   x.p2p_off = c->stage_bytes;
-  x.half_bytes = ((c->stage_bytes - kLLAreaBytes) / 2) / kUnit * kUnit;
+  x.half_bytes = ((c->stage_bytes - ll_area_of(c->stage_bytes)) / 2) / kUnit * kUnit;
   x.timeout_ns = c->timeout_ms * 1000000ull;
 }
 
@@ -486,6 +487,10 @@ static const u64 kDefChunkAR = 64ull << 20;
 static const u64 kDefChunkShard = 64ull << 20;
 static const u64 kDefChunkBcast = 64ull << 20;
 
+// LL thresholds ("ll_max_bytes" overrides both, up to the communicator's LL limit of 32 or 256 KiB)
+static const u64 kDefLLMaxAR = 32ull << 10;
+static const u64 kDefLLMaxBcast = 32ull << 10;
+
 static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
   Plan p;
   memset(&p, 0, sizeof(p));
@@ -498,14 +503,15 @@ static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
   p.op.op = op;
   p.op.avg = (op == NBD_AVG);
   p.op.world = N;
-  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kLLMaxBytes;
-  if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= kLLMaxBytes) {
+  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kDefLLMaxAR;
+  if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= c->ctx.ll_slot / 2) {
     p.op.algo = 3;  // LL one-shot: packets carry their own flags, no barrier
     p.op.chunk_bytes = bytes;
     p.op.nchunks = 1;
     u64 want = ceil_div(ceil_div(bytes, kUnit), (u64)kThreads);
-    u64 cap = emu_world > 1 ? (u64)c->num_sms / emu_world : 8;
-    if (cap > 8) cap = 8;
+    const u64 cap_real = bytes > kLLMaxBytes ? 32 : 8;  // one unit per thread up to 256 KiB
+    u64 cap = emu_world > 1 ? (u64)c->num_sms / emu_world : cap_real;
+    if (cap > cap_real) cap = cap_real;
     if (cap < 1) cap = 1;
     p.nblocks = (int)(want < 1 ? 1 : (want < cap ? want : cap));
     c->last_algo = "ar_ll";
@@ -586,14 +592,15 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
   p.op.bytes = bytes;
   p.op.root = root;
   p.op.world = N;
-  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kLLMaxBytes;
-  if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= kLLMaxBytes) {
+  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kDefLLMaxBcast;
+  if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= c->ctx.ll_slot / 2) {
     p.op.algo = 2;  // LL: packets carry their own flags, no barrier (4 KiB: ~half the latency of "direct")
     p.op.chunk_bytes = bytes;
     p.op.nchunks = 1;
     u64 want = ceil_div(ceil_div(bytes, kUnit), (u64)kThreads);
-    u64 cap = emu_world > 1 ? (u64)c->num_sms / emu_world : 8;
-    if (cap > 8) cap = 8;
+    const u64 cap_real = bytes > kLLMaxBytes ? 32 : 8;
+    u64 cap = emu_world > 1 ? (u64)c->num_sms / emu_world : cap_real;
+    if (cap > cap_real) cap = cap_real;
     if (cap < 1) cap = 1;
     p.nblocks = (int)(want < 1 ? 1 : (want < cap ? want : cap));
     c->last_algo = "bcast_ll";
@@ -2282,8 +2289,9 @@ extern "C" int nbd_plan_query(int world, size_t stage_bytes, int num_sms, int em
   c.emu = emu != 0;
   if (stage_bytes == 0) stage_bytes = kDefaultStage;
   c.stage_bytes = (stage_bytes + kStageAlign - 1) / kStageAlign * kStageAlign;
-  c.ctx.ll_off = c.stage_bytes - kLLAreaBytes;
-  c.ctx.half_bytes = ((c.stage_bytes - kLLAreaBytes) / 2) / kUnit * kUnit;
+  c.ctx.ll_off = c.stage_bytes - ll_area_of(c.stage_bytes);
+  c.ctx.ll_slot = 2 * ll_cap_of(c.stage_bytes);
+  c.ctx.half_bytes = ((c.stage_bytes - ll_area_of(c.stage_bytes)) / 2) / kUnit * kUnit;
   Plan p;
   const int ew = emu ? world : 0;
   switch (kind) {

@@ -540,3 +540,55 @@ def test_ll_broadcast_and_all_reduce_interleaved(torch_cuda, groups, world):
                 H.assert_same(H.to_numpy(t[r], "f32"), O.reduce_rank_order(x, "f32"), "f32", f"LL all_reduce rank {r}")
             else:
                 H.assert_same(H.to_numpy(t[r], "u8"), x[root], "u8", f"LL broadcast root {root} rank {r}")
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_ll_large_area_up_to_256kib(torch_cuda, world):
+    """Arenas of 64 MiB and more carry an 8 MiB LL area (limit 256 KiB per operation; the planner's
+    default threshold is lower, "ll_max_bytes" raises it).  Several units per thread: all packets
+    are sent before any is awaited.  Back-to-back all_reduces and broadcasts of 1 B .. 256 KiB,
+    in place and out of place, misaligned views, no host sync."""
+    from nbdistributed_b200 import capi
+
+    torch = torch_cuda
+    rng = np.random.default_rng(17 + world)
+    with capi.EmuGroup(world, device=0, stage_bytes=64 << 20) as grp:
+        grp.set_tunable("ll_max_bytes", 256 << 10)
+        grp.set_tunable("zero_copy_off", 1)  # emulated ranks would take 256 KiB zero-copy
+        runs = []
+        for it in range(40):
+            nbytes = (256 << 10) if it == 0 else int(rng.integers(1, 256 << 10))
+            if it % 4 == 3:
+                root = it % world
+                x = O.make_inputs(world, nbytes, "u8", seed=500 + it)
+                back = [torch.zeros(nbytes + 32, dtype=torch.uint8, device="cuda:0") for _ in range(world)]
+                off = it % 3
+                t = [b[off:off + nbytes] for b in back]
+                for v, a in zip(t, x):
+                    v.copy_(H.to_cuda(a, "u8"))
+                grp.broadcast(t, root=root)
+                assert grp.last_algo() == "bcast_ll", grp.last_algo()
+                runs.append(("bc", "u8", x, root, t))
+            else:
+                dtype = ("f32", "bf16", "i64")[it % 3]
+                n = max(1, nbytes // O.NP_DTYPE[dtype]().itemsize)
+                x = O.make_inputs(world, n, dtype, seed=500 + it)
+                t = [H.to_cuda(a, dtype) for a in x]
+                out = t if it % 2 else [torch.empty_like(a) for a in t]
+                grp.all_reduce(t, out)
+                assert grp.last_algo() == "ar_ll", grp.last_algo()
+                runs.append(("ar", dtype, x, None, out))
+        torch.cuda.synchronize()
+        grp.async_error()
+        for i, (kind, dtype, x, root, out) in enumerate(runs):
+            want = O.reduce_rank_order(x, dtype) if kind == "ar" else x[root]
+            for r in range(world):
+                H.assert_same(H.to_numpy(out[r], dtype), want, dtype, f"op {i} ({kind}) rank {r}")
+        # above the limit the planner falls back to the barrier kernels
+        x = O.make_inputs(world, (256 << 10) // 4 + 4, "f32", seed=9)
+        t = [H.to_cuda(a, "f32") for a in x]
+        grp.all_reduce(t, t)
+        assert grp.last_algo() != "ar_ll"
+        torch.cuda.synchronize()
+        for r in range(world):
+            H.assert_same(H.to_numpy(t[r], "f32"), O.reduce_rank_order(x, "f32"), "f32", f"above the limit, rank {r}")

@@ -487,9 +487,16 @@ static const u64 kDefChunkAR = 64ull << 20;
 static const u64 kDefChunkShard = 64ull << 20;
 static const u64 kDefChunkBcast = 64ull << 20;
 
-// LL thresholds ("ll_max_bytes" overrides both, up to the communicator's LL limit of 32 or 256 KiB)
-static const u64 kDefLLMaxAR = 32ull << 10;
-static const u64 kDefLLMaxBcast = 32ull << 10;
+// LL threshold ("ll_max_bytes" overrides it, up to the communicator's LL limit of 32 or 256 KiB).
+// Every rank sends 2(N-1) bytes per payload byte, so the hand-over to the barrier kernels comes
+// earlier with more ranks.  Device-side us, LL against one-shot / direct (tools/tune_ll.py,
+// profiles/r02_tune_ll_n{2,4,8}.jsonl):
+//   all_reduce  64 KiB   N=2 6.5 / 10.7   N=4  9.7 / 14.1   N=8 13.3 / 19.6
+//               128 KiB      7.6 / 11.3       10.7 / 15.0       16.9 / 19.9
+//               256 KiB      7.4 / 10.3       13.5 / 14.8       23.5 / 20.4
+//   broadcast   128 KiB      6.5 /  8.4        8.5 / 11.5       12.6 / 12.9
+//               256 KiB      7.8 /  8.4       10.4 / 11.2       18.9 / 16.4
+static u64 ll_default_max(const nbd_comm* c) { return c->world <= 4 ? (256ull << 10) : (128ull << 10); }
 
 static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
   Plan p;
@@ -503,7 +510,7 @@ static Plan plan_all_reduce(nbd_comm* c, u64 bytes, int op, int emu_world) {
   p.op.op = op;
   p.op.avg = (op == NBD_AVG);
   p.op.world = N;
-  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kDefLLMaxAR;
+  const u64 ll_max = c->t_ll_max ? c->t_ll_max : ll_default_max(c);
   if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= c->ctx.ll_slot / 2) {
     p.op.algo = 3;  // LL one-shot: packets carry their own flags, no barrier
     p.op.chunk_bytes = bytes;
@@ -592,7 +599,7 @@ static Plan plan_broadcast(nbd_comm* c, u64 bytes, int root, int emu_world) {
   p.op.bytes = bytes;
   p.op.root = root;
   p.op.world = N;
-  const u64 ll_max = c->t_ll_max ? c->t_ll_max : kDefLLMaxBcast;
+  const u64 ll_max = c->t_ll_max ? c->t_ll_max : ll_default_max(c);
   if (c->ctx.ll_off != 0 && bytes <= ll_max && bytes <= c->ctx.ll_slot / 2) {
     p.op.algo = 2;  // LL: packets carry their own flags, no barrier (4 KiB: ~half the latency of "direct")
     p.op.chunk_bytes = bytes;

@@ -24,7 +24,10 @@ def test_chunks_tile_the_message_and_fit_the_staging_half(world, stage, kind):
         assert half % UNIT == 0 and p["ll_off"] >= 2 * half
         assert 1 <= p["nblocks"] <= 512
         if (kind == "all_reduce" and p["algo"] == 3) or (kind == "broadcast" and p["algo"] == 2):
-            assert nbytes <= (32 << 10) and n == 1  # LL: no staging halves involved
+            limit = (256 << 10) if world <= 4 else (128 << 10)
+            if stage and stage < (64 << 20):
+                limit = 32 << 10  # small arenas carry the 1 MiB LL area only
+            assert nbytes <= limit and n == 1  # LL: no staging halves involved
             continue
         assert chunk % UNIT == 0 and chunk > 0
         assert n * chunk >= nbytes > (n - 1) * chunk, (nbytes, chunk, n)
@@ -47,15 +50,23 @@ def test_chunks_tile_the_message_and_fit_the_staging_half(world, stage, kind):
 
 def test_algorithm_thresholds():
     assert capi.plan_query(8, "all_reduce", 4096)["algo"] == 3            # LL
-    assert capi.plan_query(8, "all_reduce", (32 << 10) + 16)["algo"] == 1  # one-shot
+    assert capi.plan_query(8, "all_reduce", 128 << 10)["algo"] == 3        # ... up to 128 KiB beyond four ranks
+    assert capi.plan_query(8, "all_reduce", (128 << 10) + 16)["algo"] == 1  # one-shot
+    assert capi.plan_query(4, "all_reduce", 256 << 10)["algo"] == 3        # ... up to 256 KiB up to four ranks
+    assert capi.plan_query(4, "all_reduce", (256 << 10) + 16)["algo"] == 1
+    assert capi.plan_query(8, "all_reduce", (32 << 10) + 16, stage_bytes=16 << 20)["algo"] == 1  # small arena: 32 KiB LL limit
+    assert capi.plan_query(8, "all_reduce", 128 << 10)["nblocks"] == 16    # one unit per thread
     assert capi.plan_query(8, "all_reduce", 2 << 20)["algo"] == 1
     assert capi.plan_query(8, "all_reduce", (2 << 20) + 16)["algo"] == 2  # two-shot
     assert capi.plan_query(2, "all_reduce", 1 << 30)["algo"] == 1         # two ranks: always one-shot
     assert capi.plan_query(8, "broadcast", 4096)["algo"] == 2                # LL
-    assert capi.plan_query(8, "broadcast", (32 << 10) + 16)["algo"] == 0     # direct
+    assert capi.plan_query(8, "broadcast", 128 << 10)["algo"] == 2
+    assert capi.plan_query(8, "broadcast", (128 << 10) + 16)["algo"] == 0    # direct
+    assert capi.plan_query(8, "broadcast", (32 << 10) + 16, stage_bytes=16 << 20)["algo"] == 0
     assert capi.plan_query(8, "broadcast", 256 << 10)["algo"] == 0
     assert capi.plan_query(8, "broadcast", (256 << 10) + 16)["algo"] == 1
     assert capi.plan_query(2, "broadcast", 1 << 30)["algo"] == 0
+    assert capi.plan_query(2, "broadcast", 256 << 10)["algo"] == 2
     # a message that fits one chunk gets a chunk of its own (aligned) size: all CTAs have work
     p = capi.plan_query(8, "all_reduce", (16 << 20) + 4)
     assert p["nchunks"] == 1 and (16 << 20) + 4 <= p["chunk_bytes"] < (16 << 20) + 4 + 16 * 8

@@ -201,6 +201,12 @@ int nbd_all_gather(nbd_comm_t comm, const void* send, void* recv,
  * world_size*recv_count elements; recv = op over ranks of send[rank slot]. */
 int nbd_reduce_scatter(nbd_comm_t comm, const void* send, void* recv,
                        size_t recv_count, int dtype, int op, void* stream);
+/* dist.reduce_scatter(out, [in_0 .. in_{N-1}], op) — distributed_c10d.py reduce_scatter ->
+ * Backend::reduce_scatter (Backend.hpp:259): the N contributions are separate buffers of
+ * recv_count elements, sends[p] going into rank p's result.  Same result as nbd_reduce_scatter
+ * on their concatenation; nothing is concatenated. */
+int nbd_reduce_scatter_list(nbd_comm_t comm, const void* const* sends, void* recv,
+                            size_t recv_count, int dtype, int op, void* stream);
 
 /* dist.barrier() — ref:src/nbdistributed/worker.py:214 (from %sync) ->
  * Backend::barrier (Backend.hpp:382).  Enqueues a flag barrier on `stream`;
@@ -221,6 +227,10 @@ int nbd_emu_all_gather(nbd_comm_t any, const void* const* sends,
 int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends,
                            void* const* recvs, size_t recv_count, int dtype,
                            int op, void* stream);
+/* sends[r * world_size + p] = rank r's contribution to rank p's result */
+int nbd_emu_reduce_scatter_list(nbd_comm_t any, const void* const* sends,
+                                void* const* recvs, size_t recv_count, int dtype,
+                                int op, void* stream);
 int nbd_emu_barrier(nbd_comm_t any, void* stream);
 
 /* ---- many broadcasts at once ---------------------------------------------------------

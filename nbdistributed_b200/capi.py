@@ -34,6 +34,7 @@ SYMBOLS = [
     "nbd_mem_alloc", "nbd_mem_connect", "nbd_mem_free",
     "nbd_emu_create", "nbd_emu_destroy",
     "nbd_all_reduce", "nbd_broadcast", "nbd_all_gather", "nbd_reduce_scatter", "nbd_barrier",
+    "nbd_reduce_scatter_list", "nbd_emu_reduce_scatter_list",
     "nbd_emu_all_reduce", "nbd_emu_broadcast", "nbd_emu_all_gather", "nbd_emu_reduce_scatter", "nbd_emu_barrier",
     "nbd_all_reduce_host", "nbd_emu_all_reduce_host",
     "nbd_p2p_batch", "nbd_send", "nbd_recv", "nbd_emu_p2p_batch",
@@ -102,6 +103,8 @@ def load() -> C.CDLL:
         "nbd_broadcast": (i, [vp, vp, sz, i, i, vp]),
         "nbd_all_gather": (i, [vp, vp, vp, sz, i, vp]),
         "nbd_reduce_scatter": (i, [vp, vp, vp, sz, i, i, vp]),
+        "nbd_reduce_scatter_list": (i, [vp, pp, vp, sz, i, i, vp]),
+        "nbd_emu_reduce_scatter_list": (i, [vp, pp, pp, sz, i, i, vp]),
         "nbd_barrier": (i, [vp, vp]),
         "nbd_emu_all_reduce": (i, [vp, pp, pp, sz, i, i, vp]),
         "nbd_emu_broadcast": (i, [vp, pp, sz, i, i, vp]),
@@ -261,6 +264,13 @@ class EmuGroup:
         t = recvs[0]
         check(self.lib.nbd_emu_reduce_scatter(self._h, _ptr_array(sends), _ptr_array(recvs), t.numel(),
                                               torch_dtype_code(t.dtype), op, _stream_handle(stream)))
+
+    def reduce_scatter_list(self, send_lists, recvs, op: int = SUM, stream=None) -> None:
+        """send_lists[r][p] = rank r's contribution to rank p's result (separate tensors)."""
+        t = recvs[0]
+        flat = [x for row in send_lists for x in row]
+        check(self.lib.nbd_emu_reduce_scatter_list(self._h, _ptr_array(flat), _ptr_array(recvs), t.numel(),
+                                                   torch_dtype_code(t.dtype), op, _stream_handle(stream)))
 
     def barrier(self, stream=None) -> None:
         check(self.lib.nbd_emu_barrier(self._h, _stream_handle(stream)))

@@ -391,12 +391,11 @@ class BackendB200 : public c10d::Backend {
     std::vector<at::Tensor> all_in(list.begin(), list.end());
     return run(c10d::OpType::REDUCE_SCATTER, "b200:reduce_scatter", out.get_device(), all_in, {out}, opts.asyncOp,
                false, [&](cudaStream_t s) {
-                 std::vector<at::Tensor> flat_parts;
-                 flat_parts.reserve(list.size());
-                 for (auto& t : list) flat_parts.push_back(t.reshape({-1}));
-                 at::Tensor flat = at::cat(flat_parts, 0);
-                 note_stream(flat);
-                 return nbd_reduce_scatter(comm_, flat.data_ptr(), out.data_ptr(), (size_t)out.numel(), dtype, op, s);
+                 // the kernel takes the N contributions where they lie: no concatenation
+                 std::vector<const void*> parts;
+                 parts.reserve(list.size());
+                 for (auto& t : list) parts.push_back(t.data_ptr());
+                 return nbd_reduce_scatter_list(comm_, parts.data(), out.data_ptr(), (size_t)out.numel(), dtype, op, s);
                });
   }
 

@@ -93,6 +93,9 @@ template <int NCTX>
 struct Pack {
   RankCtx ctx[NCTX];
   RankBufs buf[NCTX];
+  // reduce_scatter, list form: shard[r][p] = rank r's contribution to rank p's result when the N
+  // contributions are separate buffers; all null = one contiguous send buffer (buf[r].send).
+  const char* shard[NCTX][kMaxRanks];
 };
 
 // Zero-copy collectives: every rank's user buffers are directly addressable (registered

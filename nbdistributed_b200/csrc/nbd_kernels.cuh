@@ -482,6 +482,9 @@ k_reduce_scatter(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
   if (gated_out<NCTX>(c, op)) return;
   KernelClock clk = kernel_begin(c);
   const u64 slot_stride = units_of(op.chunk_bytes) * kUnit;
+  // this rank's contribution to rank p's result: a slice of the send buffer, or its own buffer
+  const bool listed = pk.shard[ci][0] != nullptr;
+  auto shard = [&](int p) { return listed ? pk.shard[ci][p] : ub.send + (u64)p * op.bytes; };
 
   auto push = [&](u32 cidx) {
     const u64 off = (u64)cidx * op.chunk_bytes;
@@ -496,8 +499,7 @@ k_reduce_scatter(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
       for (int k = 1; k < N; ++k) {
         int p = r + k;
         if (p >= N) p -= N;
-        copy_region_to_stage<4>(c.stage[p] + half + (u64)r * slot_stride,
-                                make_region(ub.send + (u64)p * op.bytes + off, cb), base, bhi);
+        copy_region_to_stage<4>(c.stage[p] + half + (u64)r * slot_stride, make_region(shard(p) + off, cb), base, bhi);
       }
     }
   };
@@ -512,7 +514,7 @@ k_reduce_scatter(const __grid_constant__ Pack<NCTX> pk, const OpParams op) {
     const u64 half = ((clk.seq + cidx) & 1) * c.half_bytes;
     u64 lo, hi;
     block_span(units_of(op.chunk_bytes), units_of(cb), lo, hi);
-    reduce_units<T, SUM, false>(c, make_region(ub.send + (u64)r * op.bytes + off, cb), c.stage[r] + half,
+    reduce_units<T, SUM, false>(c, make_region(shard(r) + off, cb), c.stage[r] + half,
                                 slot_stride, make_region(ub.recv + off, cb), nullptr, lo, hi, op.op, op.avg);
   }
   kernel_end(c, op.nchunks, op.nchunks);

@@ -848,6 +848,7 @@ static void mute_rank(const EmuGroup* g, RankCtx* ctx) {
 
 // Fills pk for a real rank (NCTX == 1) or every emulated rank.
 static void fill_pack(Pack<1>& pk, nbd_comm* c, const void* send, void* recv) {
+  memset(pk.shard, 0, sizeof(pk.shard));
   pk.ctx[0] = c->ctx;
   pk.buf[0].send = (const char*)send;
   pk.buf[0].recv = (char*)recv;
@@ -1463,6 +1464,65 @@ int nbd_emu_reduce_scatter(nbd_comm_t any, const void* const* sends, void* const
   Plan p = plan_reduce_scatter(c0, bytes, op, g->world);
   for (int r = 1; r < g->world; ++r) g->comms[r]->last_algo = c0->last_algo;
   return launch_reduce<kMaxRanks>(K_RS, dtype, op, p.nblocks, g->world, s, pk, &p.op);
+}
+
+// reduce_scatter whose N contributions are separate buffers (c10d's list form,
+// $TORCH/.../Backend.hpp reduce_scatter(outputTensors, inputTensors)): the staged kernel takes
+// the pointers as they are, nothing is concatenated.  sends[p] = contribution to rank p's result.
+int nbd_reduce_scatter_list(nbd_comm_t c, const void* const* sends, void* recv, size_t recv_count, int dtype, int op,
+                            void* stream) {
+  int rc = check_usable(c);
+  if (rc != NBD_OK) return rc;
+  if (c->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "use nbd_emu_reduce_scatter_list with emulated communicators");
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (recv_count == 0) return NBD_OK;
+  if (!sends || !recv) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL buffer");
+  for (int p = 0; p < c->world; ++p)
+    if (!sends[p]) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL contribution for rank %d", p);
+  if (c->world == 1) return nbd_reduce_scatter(c, sends[0], recv, recv_count, dtype, op, stream);
+  DeviceGuard g(c->device);
+  const u64 bytes = (u64)recv_count * nbd_dtype_size(dtype);
+  Plan p = plan_reduce_scatter(c, bytes, op, 0);
+  Pack<1> pk;
+  fill_pack(pk, c, sends[0], recv);
+  for (int q = 0; q < c->world; ++q) pk.shard[0][q] = (const char*)sends[q];
+  c->last_algo = "reduce_scatter_list";
+  return launch_reduce<1>(K_RS, dtype, op, p.nblocks, 1, (cudaStream_t)stream, pk, &p.op);
+}
+
+// Emulated ranks: sends[r * world + p] = rank r's contribution to rank p's result.
+int nbd_emu_reduce_scatter_list(nbd_comm_t any, const void* const* sends, void* const* recvs, size_t recv_count, int dtype,
+                                int op, void* stream) {
+  int rc;
+  if ((rc = check_reduce_args(dtype, op)) != NBD_OK) return rc;
+  if (any && any->emu && recv_count == 0) return NBD_OK;
+  if (!any) return fail(NBD_ERR_INVALID_ARGUMENT, "comm is NULL");
+  if (!any->emu) return fail(NBD_ERR_INVALID_ARGUMENT, "not an emulated communicator");
+  if (!sends || !recvs) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL pointer array");
+  EmuGroup* g = any->group;
+  const int N = g->world;
+  for (int r = 0; r < N; ++r) {
+    if (!recvs[r]) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL result buffer for rank %d", r);
+    for (int p = 0; p < N; ++p)
+      if (!sends[r * N + p]) return fail(NBD_ERR_INVALID_ARGUMENT, "NULL contribution of rank %d for rank %d", r, p);
+  }
+  nbd_comm* c0 = g->comms[0];
+  DeviceGuard dg(c0->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const u64 bytes = (u64)recv_count * nbd_dtype_size(dtype);
+  if (N == 1) {
+    if (sends[0] != recvs[0]) NBD_CUDA(cudaMemcpyAsync(recvs[0], sends[0], bytes, cudaMemcpyDeviceToDevice, s));
+    return NBD_OK;
+  }
+  const void* first[kMaxRanks];
+  for (int r = 0; r < N; ++r) first[r] = sends[r * N];
+  Pack<kMaxRanks> pk;
+  if ((rc = fill_pack_emu(pk, g, first, recvs)) != NBD_OK) return rc;
+  for (int r = 0; r < N; ++r)
+    for (int p = 0; p < N; ++p) pk.shard[r][p] = (const char*)sends[r * N + p];
+  Plan p = plan_reduce_scatter(c0, bytes, op, N);
+  set_algo(c0, "reduce_scatter_list");
+  return launch_reduce<kMaxRanks>(K_RS, dtype, op, p.nblocks, N, s, pk, &p.op);
 }
 
 int nbd_emu_all_gather(nbd_comm_t any, const void* const* sends, void* const* recvs, size_t send_count, int dtype,

@@ -592,3 +592,45 @@ def test_ll_large_area_up_to_256kib(torch_cuda, world):
         torch.cuda.synchronize()
         for r in range(world):
             H.assert_same(H.to_numpy(t[r], "f32"), O.reduce_rank_order(x, "f32"), "f32", f"above the limit, rank {r}")
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("dtype,op", [("f32", "sum"), ("bf16", "sum"), ("i32", "sum"), ("f32", "max"), ("bf16", "avg"), ("u8", "bxor")])
+@pytest.mark.parametrize("numel", [1, 4099, (1 << 19) + 5])
+def test_reduce_scatter_list_form_matches_oracle(torch_cuda, groups, world, dtype, op, numel):
+    """dist.reduce_scatter(out, [in_0 .. in_{N-1}]): N separate contributions per rank, taken
+    where they lie (nbd_reduce_scatter_list) - same bits as the tensor form on their
+    concatenation, contributions untouched; every other contribution sits at a misaligned
+    address."""
+    from nbdistributed_b200 import capi
+
+    torch = torch_cuda
+    opcode = {"sum": 0, "avg": 1, "max": 4, "bxor": 7}[op]
+    grp = groups(world)
+    x = O.make_inputs(world, world * numel, dtype, seed=21)
+    itemsize = O.NP_DTYPE[dtype]().itemsize
+    lists, keep = [], []
+    for r in range(world):
+        row = []
+        for p in range(world):
+            part = np.ascontiguousarray(x[r][p * numel:(p + 1) * numel])
+            t = H.to_cuda(part, dtype)
+            if (r + p) % 2 and itemsize < 16:  # a view one element into a larger buffer
+                back = torch.empty(numel + 1, dtype=t.dtype, device="cuda:0")
+                back[1:].copy_(t)
+                keep.append(back)
+                t = back[1:]
+            row.append(t)
+        lists.append(row)
+    recvs = [torch.zeros(numel, dtype=lists[0][0].dtype, device="cuda:0") for _ in range(world)]
+    n0 = capi.launch_count()
+    grp.reduce_scatter_list(lists, recvs, op=opcode)
+    assert capi.launch_count() - n0 == 1
+    assert grp.last_algo() == "reduce_scatter_list"
+    torch.cuda.synchronize()
+    grp.async_error()
+    want = O.reduce_scatter(x, dtype, op)
+    for r in range(world):
+        H.assert_same(H.to_numpy(recvs[r], dtype), want[r], dtype, f"rank {r}")
+        for p in range(world):
+            H.assert_same(H.to_numpy(lists[r][p], dtype), x[r][p * numel:(p + 1) * numel], dtype, f"contribution {r}->{p} modified")

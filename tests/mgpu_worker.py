@@ -232,7 +232,12 @@ def body(rank: int, world: int, port: int) -> None:
         dist.reduce_scatter_tensor(o, s)
         H.assert_same(_np(o, dtype), O.reduce_scatter(xs, dtype)[rank], dtype, f"reduce_scatter_tensor {dtype} {numel}")
         o2 = torch.empty(numel, dtype=s.dtype, device=dev)
-        dist.reduce_scatter(o2, list(s.chunk(world)))
+        parts = [c.clone() for c in s.chunk(world)]  # separate allocations, as a caller's list would be
+        torch.cuda.synchronize()
+        n0 = B.launch_count()
+        dist.reduce_scatter(o2, parts)
+        torch.cuda.synchronize()
+        assert B.launch_count() - n0 == 1 and be.last_algo() == "reduce_scatter_list", (B.launch_count() - n0, be.last_algo())
         assert torch.equal(o, o2), "reduce_scatter list form differs from tensor form"
 
     # ---- symmetric memory (Backend.allocate_tensor): zero-copy kernels over NVLink ----------
